@@ -1,0 +1,135 @@
+"""The oracle restatements against golden vectors produced by the unmodified reference
+(tests/golden/make_golden.py).  CPU only."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import cases
+from oracle import mof, post, twins
+
+T = torch.from_numpy
+torch.set_grad_enabled(False)
+
+
+def close(a, b, atol, rtol=0.0):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    err = np.abs(a - b)
+    assert err.max() <= atol + rtol * np.abs(b).max(), f"max err {err.max():.3e} (ref max {np.abs(b).max():.3e})"
+
+
+def test_corr_volume_pyramid_lookup(golden):
+    g = golden("corr_lookup.npz")
+    f1, f2, coords = cases.lookup_case()
+    vol = mof.corr_volume(T(f1), T(f2))
+    close(vol[0, :2].numpy(), g["vol0"], 1e-5)
+    pyr = mof.corr_pyramid(T(f1), T(f2))
+    assert [tuple(p.shape[-2:]) for p in pyr] == [(16, 24), (8, 12), (4, 6), (2, 3)]
+    close(pyr[3][:64].numpy(), g["pyr3"], 1e-5)
+    out = mof.corr_lookup(pyr, T(coords))
+    assert out.shape == (2, 324, 16, 24) and out.is_contiguous()
+    close(out.numpy(), g["lookup"], 2e-5)
+
+
+def test_lookup_tap_order_q13():
+    """channel l*81+i*9+j samples (x+i-4, y+j-4): x offset is the slow index."""
+    h, w = 16, 24
+    f1, f2, _ = cases.lookup_case()
+    pyr = mof.corr_pyramid(T(f1[:1]), T(f2[:1]))
+    c = mof.pixel_grid(1, h, w)
+    out = mof.corr_lookup(pyr, c)
+    vol = pyr[0].view(h, w, h, w)
+    y, x, i, j = 7, 9, 6, 1
+    assert abs(out[0, i * 9 + j, y, x].item() - vol[y, x, y + j - 4, x + i - 4].item()) < 1e-5
+
+
+def test_update_block(golden, mof_weights):
+    g = golden("update_block.npz")
+    c = {k: T(v) for k, v in cases.update_case().items()}
+    Fc, _, h, w = c["net"].shape
+    attn = mof.gma_attention(c["inp"], mof_weights)
+    close(attn[:, 0, :8].numpy(), g["attn_rows"], 1e-6)
+    c0 = mof.pixel_grid(Fc, h, w)
+    close(mof.pcblock(c["fcorr"], mof_weights, "update_block.encoder.convc1", (1, 15)).numpy(), g["convc1"], 1e-4)
+    net, mhs, mask, delta = mof.update_block(c["net"], c["mhs"], c["inp"], c["fcorr"], c["bcorr"], c["fflow"],
+                                             c["bflow"], c0, attn, 1, mof_weights)
+    close(net.numpy(), g["net"], 2e-4)
+    close(mhs.numpy(), g["mhs"], 2e-4)
+    close(delta.numpy(), g["delta"], 2e-4)
+    close(mask[:, ::37].numpy(), g["mask"], 2e-2, 1e-5)
+    net, mhs, mask, delta = mof.update_block(c["net"], None, c["inp"], c["fcorr"], c["bcorr"], c["fflow"],
+                                             c["bflow"], c0, attn, 1, mof_weights)
+    close(net.numpy(), g["net_first"], 2e-4)
+    close(mhs.numpy(), g["mhs_first"], 2e-4)
+    close(delta.numpy(), g["delta_first"], 2e-4)
+
+
+def test_convex_upsample(golden):
+    fl, mk = cases.upsample_case()
+    close(mof.convex_upsample8(T(fl), T(mk)).numpy(), golden("upsample.npz")["up"], 1e-5)
+
+
+def test_twins_restatement(golden, mof_weights):
+    g = golden("twins.npz")
+    x = T(cases.twins_case())
+    close(twins.twins_svt_forward(x, mof_weights, "fnet.svt").numpy()[:, ::4], g["fnet"], 1e-4)
+    close(twins.twins_svt_forward(x, mof_weights, "cnet.svt").numpy()[:, ::4], g["cnet"], 1e-4)
+
+
+def test_mof_end_to_end_wrapper(golden, mof_weights):
+    """Full wrapper stack: window choice, /255, pad, 32 iterations, unpad, index T-2 (Q2)."""
+    g = golden("mof_e2e.npz")
+    frames = cases.mof_case()
+    win = mof.frames_to_window(frames, 2, 5)
+    flows = mof.mof_forward(mof.pad_frames(win), mof_weights)
+    close(flows.numpy()[0, :, :, ::2, ::2], g["all_flows_2"], 1e-2)
+    f2 = mof.unpad(flows, 124, 188)[0, 3].permute(1, 2, 0).numpy()
+    epe = np.sqrt(((f2 - g["flow_2"]) ** 2).sum(-1)).max()
+    assert epe < 1e-2, epe
+    f5 = mof.core_compute_flow(mof.frames_to_window(frames, 5, 5), mof_weights).permute(1, 2, 0).numpy()
+    assert np.sqrt(((f5 - g["flow_5"]) ** 2).sum(-1)).max() < 1e-2
+    u8 = cases.mof_case(as_float=False)
+    f0 = mof.core_compute_flow(mof.frames_to_window(u8, 0, 5), mof_weights).permute(1, 2, 0).numpy()
+    assert np.sqrt(((f0 - g["flow_u8_0"]) ** 2).sum(-1)).max() < 1e-2
+
+
+def test_host_logic(golden):
+    with open(os.path.join(os.path.dirname(cases.__file__), "host.json")) as f:
+        host = json.load(f)
+    for key, want in host["windows"].items():
+        n, idx, Tn = map(int, key.split(","))
+        assert mof.window_indices(n, idx, Tn) == want, key
+    for key, want in host["tiles"].items():
+        wd, ht = map(int, key.split("x"))
+        assert list(mof.tile_grid(wd, ht)) == want, key
+    assert mof.pad_amounts(436, 1024) == (0, 0, 2, 2)
+    assert mof.pad_amounts(376, 1242) == (3, 3, 0, 0)
+
+
+def test_encoders_bit_exact(golden):
+    g = golden("post.npz")
+    ff = cases.flow_field_case()
+    h, w = ff.shape[:2]
+    assert np.array_equal(post.encode_gamedev(ff, w, h), g["gamedev"])
+    assert np.array_equal(post.encode_gamedev(ff, 3840, 2160), g["gamedev_4k"])
+    assert np.array_equal(post.encode_mv_rg8(ff), g["rg8"])
+    assert np.array_equal(post.encode_mv_rg8(ff, 16.0), g["rg8_c16"])
+    assert np.array_equal(post.decode_mv_rg8(g["rg8"]), g["rg8_decoded"])
+
+
+@pytest.mark.parametrize("name,kw", [("taa_bilateral", dict(use_flow=True, use_bilateral=True)),
+                                     ("taa_bilinear", dict(use_flow=True, use_bilateral=False)),
+                                     ("taa_simple", dict(use_flow=False, use_bilateral=False))])
+def test_taa(golden, name, kw):
+    g = golden("post.npz")
+    frames, flows = cases.taa_case()
+    t = post.TAAOracle(alpha=0.1)
+    prev = None
+    for i, f in enumerate(frames):
+        o = t.apply(f, prev, alpha=0.1, seq="s", **kw)
+        want = g[f"{name}_{i}"]
+        assert o.dtype == want.dtype, (i, o.dtype, want.dtype)
+        assert np.array_equal(o, want), (name, i, np.abs(o - want).max())
+        prev = flows[i].copy()
