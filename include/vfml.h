@@ -1,0 +1,219 @@
+/*
+ * vfml.h -- C ABI of libvfml.so, the B200 (sm_100a) kernels behind the video-flow-ml
+ * optical-flow hot path.
+ *
+ * The reference has no FFI of its own on this path except the pybind module
+ * alt_cuda_corr (VideoFlow/alt_cuda_corr/correlation.cpp:51-54); everything else is
+ * PyTorch library calls made from Python.  Each entry point below cites the
+ * reference code (paths relative to the reference checkout) whose work it replaces.
+ *
+ * Rules of the boundary
+ *   - plain pointers and sizes only; all pointers are DEVICE pointers unless a
+ *     parameter is documented as host memory;
+ *   - nothing here allocates device memory or synchronises: the caller owns every
+ *     buffer (including workspaces) and the stream;
+ *   - every function returns 0 on success or a negative vfml_status; the text of
+ *     the last error of the calling thread is available from vfml_last_error();
+ *   - one host thread per stream.
+ *
+ * "rows" layout: activations of the update step are kept pixel-major
+ * ([n_rows, channels] with a row pitch in elements), i.e. NHWC.  The reference's
+ * NCHW tensors are converted at the boundary with vfml_nchw_to_rows /
+ * vfml_rows_to_nchw.
+ */
+#ifndef VFML_H
+#define VFML_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VFML_VERSION 100
+
+typedef void* vfml_stream_t; /* a cudaStream_t */
+
+enum vfml_status {
+    VFML_OK = 0,
+    VFML_ERR_ARG = -1,     /* invalid argument (null pointer, bad size, bad enum) */
+    VFML_ERR_CUDA = -2,    /* a CUDA runtime call failed; see vfml_last_error() */
+    VFML_ERR_UNSUPPORTED = -3,
+    VFML_ERR_WORKSPACE = -4 /* caller-provided workspace too small */
+};
+
+enum vfml_dtype { VFML_F32 = 0, VFML_F16 = 1 };
+
+enum vfml_layout { VFML_NCHW = 0, VFML_ROWS = 1 };
+
+int vfml_version(void);
+const char* vfml_last_error(void);
+/* Number of kernels this library has launched since it was loaded (all threads). */
+uint64_t vfml_launch_count(void);
+
+/* ---------------------------------------------------------------------------------
+ * Layout conversion.  src [n, c, hw] fp32 planar  <->  rows [n*hw, pitch] of `dtype`.
+ * Replaces the permute/contiguous/cat glue of MOFNetStack/network.py:160-170.
+ * ------------------------------------------------------------------------------- */
+int vfml_nchw_to_rows(const float* src, void* dst, int n, int c, int hw, int dst_pitch,
+                      int dst_col, int dtype, vfml_stream_t s);
+int vfml_rows_to_nchw(const void* src, float* dst, int n, int c, int hw, int src_pitch,
+                      int src_col, int dtype, vfml_stream_t s);
+
+/* ---------------------------------------------------------------------------------
+ * All-pairs correlation volume + average-pool pyramid.
+ * Replaces CorrBlock.__init__ / CorrBlock.corr, MOFNetStack/corr.py:60-74,99-107
+ * (torch.matmul / sqrt(C) followed by 3x F.avg_pool2d(2, stride=2)).
+ *
+ *   fmap1, fmap2 : [n_pairs, C, h, w] fp32 contiguous
+ *   levels[l]    : [n_pairs*h*w, h_l, w_l] of vol_dtype, h_0=h, h_{l+1} = h_l/2 (floor)
+ *   workspace    : vfml_corr_volume_workspace(...) bytes
+ * ------------------------------------------------------------------------------- */
+size_t vfml_corr_volume_workspace(int n_pairs, int C, int h, int w, int vol_dtype);
+int vfml_corr_volume_pyramid(const float* fmap1, const float* fmap2, int n_pairs, int C, int h,
+                             int w, void* const* levels, int num_levels, int vol_dtype,
+                             void* workspace, size_t workspace_bytes, vfml_stream_t s);
+
+/* ---------------------------------------------------------------------------------
+ * Multi-level (2r+1)^2 bilinear correlation lookup.
+ * Replaces CorrBlock.__call__, MOFNetStack/corr.py:76-97 + bilinear_sampler
+ * (core/utils/utils.py:62-76: grid_sample, align_corners=True, zeros padding), and the
+ * forward of alt_cuda_corr (alt_cuda_corr/correlation_kernel.cu:18-119) as a lookup.
+ *
+ *   levels[l] : as written by vfml_corr_volume_pyramid
+ *   coords    : [n_frames, 2, h, w] fp32 (channel 0 = x, 1 = y), full-resolution pixels
+ *   out       : layout VFML_NCHW -> [n_frames, L*(2r+1)^2, h, w]           (out_pitch ignored)
+ *               layout VFML_ROWS -> [n_frames*h*w, out_pitch], columns out_col..out_col+L*(2r+1)^2
+ *   channel l*(2r+1)^2 + i*(2r+1) + j samples level l at (x/2^l + i - r, y/2^l + j - r).
+ * ------------------------------------------------------------------------------- */
+int vfml_corr_lookup(const void* const* levels, int num_levels, int vol_dtype, int n_frames, int h,
+                     int w, int radius, const float* coords, void* out, int out_layout,
+                     int out_pitch, int out_col, int out_dtype, vfml_stream_t s);
+
+/* ---------------------------------------------------------------------------------
+ * Convex 8x upsampling (softmax over 9 taps fused).
+ * Replaces MOFNet.upsample_flow, MOFNetStack/network.py:97-108.
+ *   flow : [n, 2, h, w] fp32;  mask: [n, 576, h, w] fp32 (VFML_NCHW) or rows
+ *          [n*h*w, mask_pitch] starting at column mask_col (VFML_ROWS, mask_dtype)
+ *   out  : fp32, element (i, c, Y, X) at out + i*out_stride_n + c*out_stride_c + Y*out_stride_y + X
+ *          for Y in [crop_top, crop_top+out_h), X in [crop_left, crop_left+out_w) of the 8h x 8w
+ *          result, written at (Y-crop_top, X-crop_left): unpad + tile paste fused.
+ *   flow_is_coords: `flow` holds coords1; the pixel grid is subtracted on the fly (network.py:206-207).
+ * ------------------------------------------------------------------------------- */
+int vfml_convex_upsample8(const float* flow, const void* mask, int mask_layout, int mask_pitch,
+                          int mask_col, int mask_dtype, int n, int h, int w, float* out,
+                          int64_t out_stride_n, int64_t out_stride_c, int64_t out_stride_y,
+                          int crop_top, int crop_left, int out_h, int out_w, int flow_is_coords,
+                          vfml_stream_t s);
+
+/* ---------------------------------------------------------------------------------
+ * Flow encodings (bit-exact with the numpy reference given the same fp32 flow).
+ * encode_gamedev: GamedevFlowEncoder.encode, encoding/flow_encoders.py:90-117
+ * encode_mv_rg8 : MotionVectorsRG8FlowEncoder.encode, encoding/flow_encoders.py:131-153
+ *   flow [height, width, 2] fp32 -> rgb [height, width, 3] u8
+ *   norm_width/norm_height: the width/height arguments of the reference call.
+ * ------------------------------------------------------------------------------- */
+int vfml_encode_gamedev(const float* flow, uint8_t* rgb, int height, int width, float norm_width,
+                        float norm_height, float scale, float clamp, vfml_stream_t s);
+int vfml_encode_mv_rg8(const float* flow, uint8_t* rgb, int height, int width, float clamp,
+                       vfml_stream_t s);
+/* MotionVectorsRG8FlowEncoder.decode, flow_encoders.py:155-177. rgb u8 -> flow fp32 */
+int vfml_decode_mv_rg8(const uint8_t* rgb, float* flow, int height, int width, float clamp,
+                       vfml_stream_t s);
+
+/* ---------------------------------------------------------------------------------
+ * Temporal anti-aliasing, effects/taa_processor.py:41-262.
+ *   cur      : [h, w, 3] u8 current frame
+ *   flow     : [h, w, 2] fp32 (previous frame's flow, flow_processor.py:1018-1029) or NULL
+ *   history  : [h, w, 3] f64 previous output; out: [h, w, 3] f64 (may not alias history)
+ *   mode     : 0 = simple EMA (:78-80), 1 = flow + bilinear (:218-262), 2 = flow + bilateral (:149-216)
+ *   hist_f32 : 1 when the reference would hold the history as float32 at this point (frame 1 of
+ *              a sequence, and always in modes 0/1): colour weights / blends are then evaluated in
+ *              fp32 exactly as numpy's dtype promotion does; values are still stored f64.
+ * ------------------------------------------------------------------------------- */
+int vfml_taa(const uint8_t* cur, const float* flow, const double* history, double* out, int h, int w,
+             double alpha, double sigma_color, int mode, int hist_f32, vfml_stream_t s);
+/* first frame of a sequence: out = double(cur) (taa_processor.py:70-74) */
+int vfml_taa_init(const uint8_t* cur, double* out, int h, int w, vfml_stream_t s);
+
+/* ---------------------------------------------------------------------------------
+ * Building blocks of the update step (MOFNetStack/stack.py, gma.py).
+ * ------------------------------------------------------------------------------- */
+
+/* epilogue flags of vfml_gemm */
+#define VFML_EPI_BIAS 1u   /* + bias[n] */
+#define VFML_EPI_RES 2u    /* + res[m, n] */
+#define VFML_EPI_GELU 4u   /* erf GELU */
+#define VFML_EPI_RELU 8u
+#define VFML_EPI_DW1 16u   /* then v = gelu(v + dw_w[n]*v + dw_b[n]): the k=1 depthwise stage of a PCBlock */
+#define VFML_EPI_ADDTO 32u /* out += v (fp32 out only) */
+
+typedef struct vfml_gemm_desc {
+    /* D[m, n] = epi(alpha * sum_k A[m, k] * B[n, k]),  m < M, n < N, k < K */
+    const void* A;   /* [M, lda] rows, K contiguous */
+    const void* B;   /* [N, ldb] rows, K contiguous (a conv weight [Cout, Cin]) */
+    void* D;         /* [M, ldd] */
+    const float* bias;  /* [N] fp32 or NULL */
+    const void* res;    /* [M, ldr] same dtype as A, or NULL */
+    const float* dw_w;  /* [N] fp32 (VFML_EPI_DW1) */
+    const float* dw_b;  /* [N] fp32 */
+    int64_t lda, ldb, ldd, ldr;
+    int M, N, K;
+    int batch;                          /* >= 1; strides below in elements */
+    int64_t strideA, strideB, strideD, strideR;
+    float alpha;
+    uint32_t epi;
+    int in_dtype;   /* dtype of A, B, res */
+    int out_dtype;  /* dtype of D */
+} vfml_gemm_desc;
+
+/* Pointwise (1x1) convolution / matmul with fused epilogue.  Replaces the nn.Conv2d(k=1) +
+ * GELU + residual chains of PCBlock4_Deep_nopool_res (stack.py:8-32), Attention.to_qk / q.k^T
+ * (gma.py:54-74) and Aggregate's attn.v (gma.py:102-115). */
+int vfml_gemm(const vfml_gemm_desc* d, vfml_stream_t s);
+
+/* Depthwise k x k convolution over rows layout with the PCBlock residual + GELU fused:
+ *   y = gelu(x + dwconv_k(x) + b)     stack.py:25-26
+ * x, y: [n_img*h*w, pitch] (`dtype`), C channels from column 0; weight fp32 TAP-MAJOR [k*k, C]
+ * (prepacked from the checkpoint's [C, 1, k, k]), bias [C]. */
+int vfml_dwconv_res_gelu(const void* x, void* y, int n_img, int h, int w, int C, int64_t pitch_x,
+                         int64_t pitch_y, const float* weight, const float* bias, int k, int dtype,
+                         vfml_stream_t s);
+
+/* Row softmax in place-capable form: out[r, :] = softmax(in[r, :n]) (gma.py:74). in fp32. */
+int vfml_softmax_rows(const float* in, void* out, int64_t rows, int n, int64_t ld_in, int64_t ld_out,
+                      int out_dtype, vfml_stream_t s);
+
+/* Motion-encoder glue (stack.py:69-103), one launch:
+ *   flow4 = [fcoords - grid, bcoords - grid]                                  (network.py:183-184)
+ *   x400[:, 256:304] = sample(mhs of frame t+1, fcoords)  (zero state past the last frame)
+ *   x400[:, 304:352] = sample(mhs of frame t-1, bcoords)  (zero state before the first frame)
+ *   f128 = convf1_(flow4)  (1x1 conv, 4 -> 128)            written to f128 rows
+ *   mf[:, 124:128] = flow4
+ * mhs lives in x400[:, 352:400]. */
+int vfml_motion_glue(const float* fcoords, const float* bcoords, void* x400, int64_t pitch400,
+                     void* f128, int64_t pitch128, void* mf, int64_t pitch_mf, int mf_col,
+                     const float* convf1_w, const float* convf1_b, int n_frames, int h, int w,
+                     int dtype, vfml_stream_t s);
+
+/* coords[n,2,h,w] (+)= delta rows: fcoords += delta[:, 0:2]; bcoords += delta[:, 2:4] (network.py:196-197) */
+int vfml_coords_add(float* fcoords, float* bcoords, const float* delta, int64_t ld_delta, int n_frames,
+                    int hw, vfml_stream_t s);
+
+/* coords_grid, core/utils/utils.py:97-100 */
+int vfml_coords_grid(float* coords, int n, int h, int w, vfml_stream_t s);
+
+/* fill rows[:, col:col+C] with a per-channel constant (init_hidden_state broadcast, stack.py:72-73) */
+int vfml_rows_fill(void* rows, int64_t pitch, int col, int C, int64_t n_rows, const float* values,
+                   int dtype, vfml_stream_t s);
+
+/* im2col for the 3x3 mask-head convolution (stack.py:121-124): x rows [n*h*w, pitch] C channels ->
+ * out rows [n*h*w, 9*C], column (ky*3+kx)*C + c, zero padding. */
+int vfml_im2col3x3(const void* x, void* out, int n_img, int h, int w, int C, int64_t pitch_x,
+                   int64_t pitch_out, int dtype, vfml_stream_t s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VFML_H */

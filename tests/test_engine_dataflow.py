@@ -1,0 +1,36 @@
+"""Host-side orchestration of the MOF engine (buffer carving, column ranges, call order, weight
+prepacking) against the oracle, with the libvfml ops replaced by the CPU test double."""
+import numpy as np
+import torch
+
+import cases
+import fake_ops
+from oracle import mof as omof
+from oracle import twins as otwins
+from video_flow_ml_b200.mof import MOFEngine
+from video_flow_ml_b200.twins import TwinsStage01
+
+torch.set_grad_enabled(False)
+
+
+def test_twins_matches_oracle(mof_weights):
+    x = torch.from_numpy(cases.twins_case())
+    for pre in ("fnet.svt", "cnet.svt"):
+        got = TwinsStage01(mof_weights, pre, "cpu")(x)
+        want = otwins.twins_svt_forward(x, mof_weights, pre)
+        assert (got - want).abs().max() < 1e-4
+
+
+def test_engine_dataflow_matches_oracle(mof_weights):
+    frames = cases.mof_case()
+    win = omof.pad_frames(omof.frames_to_window(frames, 2, 5)).contiguous()
+    eng = MOFEngine(mof_weights, "cpu", torch.float32, iters=3, ops=fake_ops)
+    fmaps, net, inp = eng.encode(win)
+    of, on, oi = omof.mof_encode(win, mof_weights)
+    assert (fmaps - of).abs().max() < 1e-4 and (net - on).abs().max() < 1e-4 and (inp - oi).abs().max() < 1e-4
+    want = omof.mof_refine(of, on, oi, mof_weights, iters=3)
+    got = eng.refine(of, on, oi)
+    assert got.shape == want.shape
+    assert (got - want).abs().max() < 2e-3, (got - want).abs().max()
+    sel = eng.refine(of, on, oi, select=3, crop=(2, 1, 120, 180))
+    assert (sel - want[0, 3, :, 2:122, 1:181]).abs().max() < 2e-3

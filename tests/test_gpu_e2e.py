@@ -1,0 +1,110 @@
+"""End-to-end parity of the CUDA path (through the drop-in wrappers and the C ABI) against the golden
+outputs of the unmodified reference wrapper stack (tests/golden/mof_e2e.npz).  pytest -m gpu."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import cases
+from oracle import mof as omof
+
+pytestmark = pytest.mark.gpu
+
+
+def epe(a, b):
+    return np.sqrt(((a - b) ** 2).sum(-1)).max()
+
+
+@pytest.fixture(scope="module")
+def processor(mof_weights):
+    from video_flow_ml_b200.processing import VideoFlowProcessor
+    p = VideoFlowProcessor("cuda", sequence_length=5, precision="fp32")
+    with pytest.raises(RuntimeError):
+        p.compute_optical_flow([np.zeros((64, 64, 3), np.uint8)] * 5, 0)
+    p.core.load_state_dict({"module." + k: v for k, v in mof_weights.items()})
+    return p
+
+
+def test_mof_fp32_matches_reference_golden(processor, golden):
+    """32 iterations, fp32 tier: max EPE delta <= 1e-2 px vs the reference's own output."""
+    g = golden("mof_e2e.npz")
+    frames = cases.mof_case()
+    for idx in (2, 5):
+        flow = processor.compute_optical_flow(list(frames), idx)
+        assert flow.shape == (124, 188, 2) and flow.dtype == np.float32
+        assert epe(flow, g[f"flow_{idx}"]) <= 1e-2, (idx, epe(flow, g[f"flow_{idx}"]))
+    u8 = cases.mof_case(as_float=False)
+    f0 = processor.compute_optical_flow(list(u8), 0)
+    assert epe(f0, g["flow_u8_0"]) <= 1e-2
+
+
+def test_mof_all_flows_match_reference_golden(processor, golden):
+    g = golden("mof_e2e.npz")
+    win = processor.prepare_frame_sequence(list(cases.mof_case()), 2)
+    flows = processor.core.model.forward(omof.pad_frames(win.cpu()).cuda())
+    assert flows.shape == (1, 6, 2, 128, 192)
+    err = np.abs(flows.cpu().numpy()[0, :, :, ::2, ::2] - g["all_flows_2"]).max()
+    assert err <= 1e-2, err
+
+
+def test_core_validation_errors(processor):
+    core = processor.core
+    with pytest.raises(ValueError):
+        core.compute_flow_from_tensor(np.zeros((1, 5, 3, 64, 64), np.float32))
+    with pytest.raises(ValueError):
+        core.compute_flow_from_tensor(torch.zeros((1, 5, 3, 64, 64)))             # CPU tensor
+    with pytest.raises(ValueError):
+        core.compute_flow_from_tensor(torch.zeros((5, 3, 64, 64), device="cuda"))
+    with pytest.raises(ValueError):
+        core.compute_flow_from_tensor(torch.zeros((2, 5, 3, 64, 64), device="cuda"))
+    with pytest.raises(ValueError):
+        core.compute_flow_from_tensor(torch.zeros((1, 5, 4, 64, 64), device="cuda"))
+    assert core.get_model_info()["status"] == "loaded"
+
+
+def test_tiled_equals_per_tile_clips(processor):
+    """Tile mode = independent clips per disjoint tile, pasted (reference :231-283).  Uses a small tile
+    size through calculate_tile_grid's parameter by monkeypatching the default."""
+    frames = cases.synthetic_clip(5, 192, 352, seed=5)
+    orig = processor.calculate_tile_grid
+    processor.calculate_tile_grid = lambda w, h, tile_size=96: orig(w, h, tile_size)
+    processor.set_tile_mode(True)
+    iters = processor.core.model.iters
+    processor.core.model.iters = 4
+    try:
+        full = processor.compute_optical_flow_tiled(frames, 2)
+        assert full.shape == (192, 352, 2)
+        processor.set_tile_mode(False)
+        for ti in orig(352, 192, 96)[4]:
+            x, y, w, h = ti['x'], ti['y'], ti['width'], ti['height']
+            tile = processor.compute_optical_flow([f[y:y + h, x:x + w] for f in frames], 2)
+            assert np.abs(full[y:y + h, x:x + w] - tile).max() < 1e-4
+    finally:
+        processor.calculate_tile_grid = orig
+        processor.set_tile_mode(False)
+        processor.core.model.iters = iters
+
+
+def test_post_pass_wrappers(golden):
+    from video_flow_ml_b200.effects import TAAProcessor
+    from video_flow_ml_b200.encoding import encode_flow, FlowEncoderFactory
+    g = golden("post.npz")
+    ff = cases.flow_field_case()
+    assert np.array_equal(encode_flow(ff.copy(), ff.shape[1], ff.shape[0], "gamedev"), g["gamedev"])
+    enc = FlowEncoderFactory.create_encoder("motion-vectors-rg8", clamp_range=16.0)
+    assert np.array_equal(enc.encode(ff, 0, 0), g["rg8_c16"])
+    with pytest.raises(ValueError):
+        FlowEncoderFactory.create_encoder("nope")
+    frames, flows = cases.taa_case()
+    for name, kw in (("taa_bilateral", dict(use_flow=True, use_bilateral=True)),
+                     ("taa_bilinear", dict(use_flow=True, use_bilateral=False)),
+                     ("taa_simple", dict(use_flow=False, use_bilateral=False))):
+        t = TAAProcessor(alpha=0.1)
+        prev = None
+        for i, f in enumerate(frames):
+            o = t.apply_taa(f, prev, alpha=0.1, sequence_id="s", **kw)
+            want = g[f"{name}_{i}"]
+            assert o.dtype == want.dtype, (name, i, o.dtype, want.dtype)
+            assert np.abs(o.astype(np.float64) - want).max() <= 1e-3, (name, i)
+            prev = flows[i].copy()

@@ -1,0 +1,22 @@
+// Library-level entry points of libvfml: version, per-thread last error, launch counter.
+#include <stdarg.h>
+
+#include "common.cuh"
+
+namespace vfml {
+
+static thread_local char g_err[512] = "";
+std::atomic<uint64_t> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+}  // namespace vfml
+
+extern "C" int vfml_version(void) { return VFML_VERSION; }
+extern "C" const char* vfml_last_error(void) { return vfml::g_err; }
+extern "C" uint64_t vfml_launch_count(void) { return vfml::g_launches.load(); }

@@ -1,0 +1,369 @@
+// Non-GEMM pieces of the MOF update step in rows (NHWC) layout: layout conversion, depthwise
+// convolution with fused residual + GELU, row softmax, the motion-encoder glue (flow
+// differences, temporal hidden-state warp, convf1_), coordinate update, im2col for the mask head.
+//
+// MOFNetStack/stack.py:8-32 (PCBlock depthwise stage), :69-103 (motion encoder),
+// gma.py:74 (softmax), network.py:183-197 (flow = coords1 - coords0, coords += delta).
+#include "common.cuh"
+
+namespace vfml {
+
+// ---------------------------------------------------------------- layout conversion
+template <typename T>
+__global__ void nchw_to_rows_kernel(const float* __restrict__ src, T* __restrict__ dst, int c, int hw,
+                                    int64_t pitch, int col) {
+    __shared__ float tile[32][33];
+    const int n = blockIdx.z;
+    const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+    const int tx = threadIdx.x, ty = threadIdx.y;   // 32 x 8
+    for (int i = ty; i < 32; i += 8) {
+        const int ch = c0 + i, p = p0 + tx;
+        tile[i][tx] = (ch < c && p < hw) ? src[((int64_t)n * c + ch) * hw + p] : 0.0f;
+    }
+    __syncthreads();
+    for (int i = ty; i < 32; i += 8) {
+        const int p = p0 + i, ch = c0 + tx;
+        if (p < hw && ch < c) dst[((int64_t)n * hw + p) * pitch + col + ch] = from_f32<T>(tile[tx][i]);
+    }
+}
+
+template <typename T>
+__global__ void rows_to_nchw_kernel(const T* __restrict__ src, float* __restrict__ dst, int c, int hw,
+                                    int64_t pitch, int col) {
+    __shared__ float tile[32][33];
+    const int n = blockIdx.z;
+    const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    for (int i = ty; i < 32; i += 8) {
+        const int p = p0 + i, ch = c0 + tx;
+        tile[i][tx] = (p < hw && ch < c) ? to_f32<T>(src[((int64_t)n * hw + p) * pitch + col + ch]) : 0.0f;
+    }
+    __syncthreads();
+    for (int i = ty; i < 32; i += 8) {
+        const int ch = c0 + i, p = p0 + tx;
+        if (ch < c && p < hw) dst[((int64_t)n * c + ch) * hw + p] = tile[tx][i];
+    }
+}
+
+// ---------------------------------------------------------------- depthwise conv + residual + GELU
+// thread per (pixel, channel), channel fastest; weights tap-major [k*k][C] so both loads coalesce.
+template <typename T>
+__global__ void __launch_bounds__(256)
+dwconv_res_gelu_kernel(const T* __restrict__ x, T* __restrict__ y, int n_img, int h, int w, int C,
+                       int64_t px, int64_t py, const float* __restrict__ wgt, const float* __restrict__ bias, int k) {
+    const int64_t total = (int64_t)n_img * h * w * C;
+    const int r = k / 2;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(t % C);
+        const int64_t row = t / C;
+        const int xx = (int)(row % w);
+        const int yy = (int)((row / w) % h);
+        const int64_t img_row0 = row - ((int64_t)yy * w + xx);
+        float acc = 0.0f;
+        for (int ky = 0; ky < k; ++ky) {
+            const int sy = yy + ky - r;
+            if (sy < 0 || sy >= h) continue;
+            for (int kx = 0; kx < k; ++kx) {
+                const int sx = xx + kx - r;
+                if (sx < 0 || sx >= w) continue;
+                acc = fmaf(to_f32<T>(x[(img_row0 + (int64_t)sy * w + sx) * px + c]), __ldg(wgt + (ky * k + kx) * C + c), acc);
+            }
+        }
+        const float v = to_f32<T>(x[row * px + c]) + (acc + __ldg(bias + c));
+        y[row * py + c] = from_f32<T>(gelu_erf(v));
+    }
+}
+
+// ---------------------------------------------------------------- row softmax
+template <typename TO>
+__global__ void __launch_bounds__(256)
+softmax_rows_kernel(const float* __restrict__ in, TO* __restrict__ out, int n, int64_t ld_in, int64_t ld_out) {
+    __shared__ float red[8];
+    __shared__ float bcast;
+    const float* src = in + blockIdx.x * ld_in;
+    TO* dst = out + blockIdx.x * ld_out;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float mx = -INFINITY;
+    for (int i = threadIdx.x; i < n; i += 256) mx = fmaxf(mx, src[i]);
+    for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) red[warp] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float m = red[0];
+        for (int i = 1; i < 8; ++i) m = fmaxf(m, red[i]);
+        bcast = m;
+    }
+    __syncthreads();
+    mx = bcast;
+    float sum = 0.0f;
+    for (int i = threadIdx.x; i < n; i += 256) sum += expf(src[i] - mx);
+    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    __syncthreads();
+    if (lane == 0) red[warp] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float s = 0.0f;
+        for (int i = 0; i < 8; ++i) s += red[i];
+        bcast = s;
+    }
+    __syncthreads();
+    const float inv = 1.0f / bcast;
+    for (int i = threadIdx.x; i < n; i += 256) dst[i] = from_f32<TO>(expf(src[i] - mx) * inv);
+}
+
+// ---------------------------------------------------------------- motion-encoder glue
+struct GlueParams {
+    const float* fc; const float* bc;
+    void* x400; int64_t p400;
+    void* f128; int64_t p128;
+    void* mf; int64_t pmf; int mf_col;
+    const float* w1; const float* b1;   // convf1_: [128, 4], [128]
+    int F, h, w;
+};
+
+template <typename T>
+__device__ __forceinline__ void warp_state(const T* x400, int64_t p400, int frame, int F, int h, int w, float sx, float sy,
+                                           T* dst, int lane) {
+    // bilinear_sampler, zeros padding, align_corners=True (core/utils/utils.py:62-76) over the 48-channel
+    // hidden state of `frame` (zero state outside the window, stack.py:75-80)
+    float acc0 = 0.0f, acc1 = 0.0f;   // channels lane, lane + 32 (< 48)
+    if (frame >= 0 && frame < F && sx == sx && sy == sy) {
+        sx = fminf(fmaxf(sx, -1.0e6f), 1.0e6f);
+        sy = fminf(fmaxf(sy, -1.0e6f), 1.0e6f);
+        const float flx = floorf(sx), fly = floorf(sy);
+        const float wx1 = sx - flx, wy1 = sy - fly;
+        const int x0 = (int)flx, y0 = (int)fly;
+        const T* base = x400 + (int64_t)frame * h * w * p400 + 352;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int gx = x0 + (t & 1), gy = y0 + (t >> 1);
+            if (gx < 0 || gx >= w || gy < 0 || gy >= h) continue;
+            const float wgt = ((t & 1) ? wx1 : 1.0f - wx1) * ((t >> 1) ? wy1 : 1.0f - wy1);
+            const T* src = base + ((int64_t)gy * w + gx) * p400;
+            acc0 += wgt * to_f32<T>(src[lane]);
+            if (lane < 16) acc1 += wgt * to_f32<T>(src[lane + 32]);
+        }
+    }
+    dst[lane] = from_f32<T>(acc0);
+    if (lane < 16) dst[lane + 32] = from_f32<T>(acc1);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) motion_glue_kernel(const GlueParams p) {
+    const int lane = threadIdx.x & 31;
+    const int P = p.h * p.w;
+    const int64_t total = (int64_t)p.F * P;
+    const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    T* x400 = reinterpret_cast<T*>(p.x400);
+    for (int64_t row = warp0; row < total; row += nwarps) {
+        const int f = (int)(row / P);
+        const int pix = (int)(row - (int64_t)f * P);
+        const int y = pix / p.w, x = pix - y * p.w;
+        const float fcx = __ldg(p.fc + ((int64_t)f * 2) * P + pix), fcy = __ldg(p.fc + ((int64_t)f * 2 + 1) * P + pix);
+        const float bcx = __ldg(p.bc + ((int64_t)f * 2) * P + pix), bcy = __ldg(p.bc + ((int64_t)f * 2 + 1) * P + pix);
+        const float fl[4] = {fcx - (float)x, fcy - (float)y, bcx - (float)x, bcy - (float)y};
+        T* xrow = x400 + row * p.p400;
+        warp_state<T>(x400, p.p400, f + 1, p.F, p.h, p.w, fcx, fcy, xrow + 256, lane);
+        warp_state<T>(x400, p.p400, f - 1, p.F, p.h, p.w, bcx, bcy, xrow + 304, lane);
+        T* frow = reinterpret_cast<T*>(p.f128) + row * p.p128;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int o = lane + 32 * q;
+            const float4 wv = __ldg(reinterpret_cast<const float4*>(p.w1) + o);
+            float v = __ldg(p.b1 + o);
+            v = fmaf(wv.x, fl[0], v);
+            v = fmaf(wv.y, fl[1], v);
+            v = fmaf(wv.z, fl[2], v);
+            v = fmaf(wv.w, fl[3], v);
+            frow[o] = from_f32<T>(v);
+        }
+        if (lane < 4) reinterpret_cast<T*>(p.mf)[row * p.pmf + p.mf_col + 124 + lane] = from_f32<T>(fl[lane]);
+    }
+}
+
+__global__ void coords_add_kernel(float* __restrict__ fc, float* __restrict__ bc, const float* __restrict__ delta,
+                                  int64_t ld, int F, int hw) {
+    const int64_t total = (int64_t)F * hw;
+    for (int64_t row = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; row < total; row += (int64_t)gridDim.x * blockDim.x) {
+        const int f = (int)(row / hw);
+        const int pix = (int)(row - (int64_t)f * hw);
+        const float4 d = *reinterpret_cast<const float4*>(delta + row * ld);
+        fc[((int64_t)f * 2) * hw + pix] += d.x;
+        fc[((int64_t)f * 2 + 1) * hw + pix] += d.y;
+        bc[((int64_t)f * 2) * hw + pix] += d.z;
+        bc[((int64_t)f * 2 + 1) * hw + pix] += d.w;
+    }
+}
+
+__global__ void coords_grid_kernel(float* __restrict__ c, int n, int h, int w) {
+    const int64_t total = (int64_t)n * 2 * h * w;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int x = (int)(t % w);
+        const int y = (int)((t / w) % h);
+        const int ch = (int)((t / ((int64_t)w * h)) % 2);
+        c[t] = ch == 0 ? (float)x : (float)y;
+    }
+}
+
+template <typename T>
+__global__ void rows_fill_kernel(T* __restrict__ rows, int64_t pitch, int col, int C, int64_t n_rows, const float* __restrict__ v) {
+    const int64_t total = n_rows * C;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(t % C);
+        rows[(t / C) * pitch + col + c] = from_f32<T>(v[c]);
+    }
+}
+
+template <typename T>
+__global__ void im2col3x3_kernel(const T* __restrict__ x, T* __restrict__ out, int n_img, int h, int w, int C,
+                                 int64_t px, int64_t po) {
+    const int64_t total = (int64_t)n_img * h * w * 9 * C;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(t % C);
+        const int tap = (int)((t / C) % 9);
+        const int64_t row = t / ((int64_t)9 * C);
+        const int xx = (int)(row % w), yy = (int)((row / w) % h);
+        const int sy = yy + tap / 3 - 1, sx = xx + tap % 3 - 1;
+        T v = from_f32<T>(0.0f);
+        if (sy >= 0 && sy < h && sx >= 0 && sx < w) v = x[(row + (int64_t)(sy - yy) * w + (sx - xx)) * px + c];
+        out[row * po + tap * C + c] = v;
+    }
+}
+
+static inline int ew_blocks(int64_t n) { return (int)std::min<int64_t>((n + 255) / 256, 148 * 32); }
+
+int gemm_ffma(const vfml_gemm_desc& d, cudaStream_t st);
+int validate_gemm(const vfml_gemm_desc* d);
+
+}  // namespace vfml
+
+using namespace vfml;
+
+#define DISPATCH_T(dtype, CALL_F32, CALL_F16) \
+    do {                                      \
+        if ((dtype) == VFML_F32) { CALL_F32; } \
+        else { CALL_F16; }                    \
+    } while (0)
+
+extern "C" int vfml_nchw_to_rows(const float* src, void* dst, int n, int c, int hw, int dst_pitch, int dst_col,
+                                 int dtype, vfml_stream_t s) {
+    VFML_REQUIRE(n >= 0 && c >= 0 && hw >= 0 && dst_col >= 0 && dst_pitch >= dst_col + c, "nchw_to_rows: bad shape");
+    VFML_REQUIRE(valid_dtype(dtype), "nchw_to_rows: bad dtype");
+    if ((int64_t)n * c * hw == 0) return VFML_OK;
+    VFML_REQUIRE(src && dst, "nchw_to_rows: null pointer");
+    dim3 grid(cdiv(hw, 32), cdiv(c, 32), n), block(32, 8);
+    DISPATCH_T(dtype, (nchw_to_rows_kernel<float><<<grid, block, 0, to_stream(s)>>>(src, (float*)dst, c, hw, dst_pitch, dst_col)),
+               (nchw_to_rows_kernel<__half><<<grid, block, 0, to_stream(s)>>>(src, (__half*)dst, c, hw, dst_pitch, dst_col)));
+    VFML_LAUNCH_CHECK("nchw_to_rows");
+    return VFML_OK;
+}
+
+extern "C" int vfml_rows_to_nchw(const void* src, float* dst, int n, int c, int hw, int src_pitch, int src_col,
+                                 int dtype, vfml_stream_t s) {
+    VFML_REQUIRE(n >= 0 && c >= 0 && hw >= 0 && src_col >= 0 && src_pitch >= src_col + c, "rows_to_nchw: bad shape");
+    VFML_REQUIRE(valid_dtype(dtype), "rows_to_nchw: bad dtype");
+    if ((int64_t)n * c * hw == 0) return VFML_OK;
+    VFML_REQUIRE(src && dst, "rows_to_nchw: null pointer");
+    dim3 grid(cdiv(hw, 32), cdiv(c, 32), n), block(32, 8);
+    DISPATCH_T(dtype, (rows_to_nchw_kernel<float><<<grid, block, 0, to_stream(s)>>>((const float*)src, dst, c, hw, src_pitch, src_col)),
+               (rows_to_nchw_kernel<__half><<<grid, block, 0, to_stream(s)>>>((const __half*)src, dst, c, hw, src_pitch, src_col)));
+    VFML_LAUNCH_CHECK("rows_to_nchw");
+    return VFML_OK;
+}
+
+extern "C" int vfml_gemm(const vfml_gemm_desc* d, vfml_stream_t s) {
+    int rc = validate_gemm(d);
+    if (rc) return rc;
+    if (d->M == 0 || d->N == 0) return VFML_OK;
+    return gemm_ffma(*d, to_stream(s));
+}
+
+extern "C" int vfml_dwconv_res_gelu(const void* x, void* y, int n_img, int h, int w, int C, int64_t pitch_x,
+                                    int64_t pitch_y, const float* weight, const float* bias, int k, int dtype,
+                                    vfml_stream_t s) {
+    VFML_REQUIRE(n_img >= 0 && h > 0 && w > 0 && C > 0 && pitch_x >= C && pitch_y >= C, "dwconv: bad shape");
+    VFML_REQUIRE(k >= 1 && (k & 1), "dwconv: kernel size %d must be odd", k);
+    VFML_REQUIRE(valid_dtype(dtype), "dwconv: bad dtype");
+    if (n_img == 0) return VFML_OK;
+    VFML_REQUIRE(x && y && weight && bias && x != y, "dwconv: null or aliased pointer");
+    const int64_t total = (int64_t)n_img * h * w * C;
+    DISPATCH_T(dtype, (dwconv_res_gelu_kernel<float><<<ew_blocks(total), 256, 0, to_stream(s)>>>((const float*)x, (float*)y, n_img, h, w, C, pitch_x, pitch_y, weight, bias, k)),
+               (dwconv_res_gelu_kernel<__half><<<ew_blocks(total), 256, 0, to_stream(s)>>>((const __half*)x, (__half*)y, n_img, h, w, C, pitch_x, pitch_y, weight, bias, k)));
+    VFML_LAUNCH_CHECK("dwconv_res_gelu");
+    return VFML_OK;
+}
+
+extern "C" int vfml_softmax_rows(const float* in, void* out, int64_t rows, int n, int64_t ld_in, int64_t ld_out,
+                                 int out_dtype, vfml_stream_t s) {
+    VFML_REQUIRE(rows >= 0 && n > 0 && ld_in >= n && ld_out >= n, "softmax_rows: bad shape");
+    VFML_REQUIRE(valid_dtype(out_dtype), "softmax_rows: bad dtype");
+    if (rows == 0) return VFML_OK;
+    VFML_REQUIRE(in && out, "softmax_rows: null pointer");
+    VFML_REQUIRE(rows <= 2147483647LL, "softmax_rows: too many rows");
+    DISPATCH_T(out_dtype, (softmax_rows_kernel<float><<<(unsigned)rows, 256, 0, to_stream(s)>>>(in, (float*)out, n, ld_in, ld_out)),
+               (softmax_rows_kernel<__half><<<(unsigned)rows, 256, 0, to_stream(s)>>>(in, (__half*)out, n, ld_in, ld_out)));
+    VFML_LAUNCH_CHECK("softmax_rows");
+    return VFML_OK;
+}
+
+extern "C" int vfml_motion_glue(const float* fcoords, const float* bcoords, void* x400, int64_t pitch400, void* f128,
+                                int64_t pitch128, void* mf, int64_t pitch_mf, int mf_col, const float* convf1_w,
+                                const float* convf1_b, int n_frames, int h, int w, int dtype, vfml_stream_t s) {
+    VFML_REQUIRE(n_frames >= 0 && h > 0 && w > 0, "motion_glue: bad shape");
+    VFML_REQUIRE(pitch400 >= 400 && pitch128 >= 128 && mf_col >= 0 && pitch_mf >= mf_col + 128, "motion_glue: bad pitch");
+    VFML_REQUIRE(valid_dtype(dtype), "motion_glue: bad dtype");
+    if (n_frames == 0) return VFML_OK;
+    VFML_REQUIRE(fcoords && bcoords && x400 && f128 && mf && convf1_w && convf1_b, "motion_glue: null pointer");
+    GlueParams p{fcoords, bcoords, x400, pitch400, f128, pitch128, mf, pitch_mf, mf_col, convf1_w, convf1_b, n_frames, h, w};
+    const int64_t total = (int64_t)n_frames * h * w;
+    const int blocks = (int)std::min<int64_t>(cdiv(total, 8), 148 * 16);
+    DISPATCH_T(dtype, (motion_glue_kernel<float><<<blocks, 256, 0, to_stream(s)>>>(p)),
+               (motion_glue_kernel<__half><<<blocks, 256, 0, to_stream(s)>>>(p)));
+    VFML_LAUNCH_CHECK("motion_glue");
+    return VFML_OK;
+}
+
+extern "C" int vfml_coords_add(float* fcoords, float* bcoords, const float* delta, int64_t ld_delta, int n_frames,
+                               int hw, vfml_stream_t s) {
+    VFML_REQUIRE(n_frames >= 0 && hw >= 0 && ld_delta >= 4 && (ld_delta % 4) == 0, "coords_add: bad shape (ld %% 4 == 0)");
+    if ((int64_t)n_frames * hw == 0) return VFML_OK;
+    VFML_REQUIRE(fcoords && bcoords && delta, "coords_add: null pointer");
+    coords_add_kernel<<<ew_blocks((int64_t)n_frames * hw), 256, 0, to_stream(s)>>>(fcoords, bcoords, delta, ld_delta, n_frames, hw);
+    VFML_LAUNCH_CHECK("coords_add");
+    return VFML_OK;
+}
+
+extern "C" int vfml_coords_grid(float* coords, int n, int h, int w, vfml_stream_t s) {
+    VFML_REQUIRE(n >= 0 && h >= 0 && w >= 0, "coords_grid: bad shape");
+    if ((int64_t)n * h * w == 0) return VFML_OK;
+    VFML_REQUIRE(coords, "coords_grid: null pointer");
+    coords_grid_kernel<<<ew_blocks((int64_t)n * 2 * h * w), 256, 0, to_stream(s)>>>(coords, n, h, w);
+    VFML_LAUNCH_CHECK("coords_grid");
+    return VFML_OK;
+}
+
+extern "C" int vfml_rows_fill(void* rows, int64_t pitch, int col, int C, int64_t n_rows, const float* values, int dtype,
+                              vfml_stream_t s) {
+    VFML_REQUIRE(n_rows >= 0 && C >= 0 && col >= 0 && pitch >= col + C, "rows_fill: bad shape");
+    VFML_REQUIRE(valid_dtype(dtype), "rows_fill: bad dtype");
+    if (n_rows * C == 0) return VFML_OK;
+    VFML_REQUIRE(rows && values, "rows_fill: null pointer");
+    DISPATCH_T(dtype, (rows_fill_kernel<float><<<ew_blocks(n_rows * C), 256, 0, to_stream(s)>>>((float*)rows, pitch, col, C, n_rows, values)),
+               (rows_fill_kernel<__half><<<ew_blocks(n_rows * C), 256, 0, to_stream(s)>>>((__half*)rows, pitch, col, C, n_rows, values)));
+    VFML_LAUNCH_CHECK("rows_fill");
+    return VFML_OK;
+}
+
+extern "C" int vfml_im2col3x3(const void* x, void* out, int n_img, int h, int w, int C, int64_t pitch_x, int64_t pitch_out,
+                              int dtype, vfml_stream_t s) {
+    VFML_REQUIRE(n_img >= 0 && h > 0 && w > 0 && C > 0 && pitch_x >= C && pitch_out >= 9 * C, "im2col3x3: bad shape");
+    VFML_REQUIRE(valid_dtype(dtype), "im2col3x3: bad dtype");
+    if (n_img == 0) return VFML_OK;
+    VFML_REQUIRE(x && out, "im2col3x3: null pointer");
+    const int64_t total = (int64_t)n_img * h * w * 9 * C;
+    DISPATCH_T(dtype, (im2col3x3_kernel<float><<<ew_blocks(total), 256, 0, to_stream(s)>>>((const float*)x, (float*)out, n_img, h, w, C, pitch_x, pitch_out)),
+               (im2col3x3_kernel<__half><<<ew_blocks(total), 256, 0, to_stream(s)>>>((const __half*)x, (__half*)out, n_img, h, w, C, pitch_x, pitch_out)));
+    VFML_LAUNCH_CHECK("im2col3x3");
+    return VFML_OK;
+}

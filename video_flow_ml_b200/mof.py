@@ -1,0 +1,262 @@
+"""VideoFlow MOF (multi-frame) inference engine on libvfml kernels.
+
+Mirrors MOFNet.forward (VideoFlow/core/Networks/MOFNetStack/network.py:138-215) for eval:
+encoders -> two all-pairs correlation pyramids -> GMA attention -> 32 x {2 lookups, motion
+encoder, aggregate, PC-block "GRU", flow head} -> mask head + convex 8x upsampling.
+
+Differences from the reference that do not change results: the mask head and the
+upsampling run on the last iteration only, and ``select`` lets the caller upsample only the
+flow it consumes.  All activations of the update step live in pixel-major "rows" buffers
+(NHWC) so that every 1x1 convolution is a plain K-contiguous GEMM and every ``torch.cat`` of
+the reference is just a column range of a wider buffer.
+
+Weights use the upstream checkpoint key names (``update_block.encoder.convc1.ffn1.0.weight``,
+``att.to_qk.weight`` ...).  ``dtype`` selects the tier: float32 (exact fp32 FFMA kernels,
+<= 1e-2 px vs the fp32 reference) or float16 (tensor-core tier; the reference itself runs
+this part under fp16 autocast, network.py:149-192).
+"""
+import torch
+
+from . import ops as _ops
+from .twins import TwinsStage01
+
+ITERS = 32          # VideoFlow/configs/multiframes_sintel_submission.py:36 (decoder_depth)
+CORR_LEVELS = 4
+CORR_RADIUS = 4     # forced, network.py:23
+
+
+def _pad8(c):
+    return (c + 7) // 8 * 8
+
+
+class _PCWeights:
+    """PCBlock4_Deep_nopool_res parameters (stack.py:8-32) prepacked for the kernels."""
+
+    def __init__(self, sd, p, k, dev, dt):
+        g = lambda n: sd[f"{p}.{n}"].to(dev)
+        mat = lambda n: g(n + ".weight").flatten(1).to(dt).contiguous()
+        vec = lambda n: g(n + ".bias").float().contiguous()
+        self.k = k
+        self.w1a, self.b1a = mat("ffn1.0"), vec("ffn1.0")
+        self.w1b, self.b1b = mat("ffn1.2"), vec("ffn1.2")
+        self.dw1_w = g("conv_list.0.weight").float().flatten().contiguous()      # k = 1 depthwise
+        self.dw1_b = vec("conv_list.0")
+        C = self.dw1_w.numel()
+        self.dwk_w = g("conv_list.1.weight").float().reshape(C, k * k).t().contiguous()   # tap-major [k*k, C]
+        self.dwk_b = vec("conv_list.1")
+        self.wpw, self.bpw = mat("pw"), vec("pw")
+        self.w2a, self.b2a = mat("ffn2.0"), vec("ffn2.0")
+        self.w2b, self.b2b = mat("ffn2.2"), vec("ffn2.2")
+        self.cin, self.hid, self.cout = C, self.w1a.shape[0], self.w2b.shape[0]
+
+
+class MOFEngine:
+    """Stateless-per-window MOF refinement; buffers are cached per (F, h, w)."""
+
+    def __init__(self, state_dict, device, dtype=torch.float32, iters=ITERS, ops=None, encoder_dtype=None):
+        self.ops = ops or _ops
+        self.dev = torch.device(device)
+        self.dt = dtype
+        self.iters = iters
+        sd = {k[7:] if k.startswith("module.") else k: v for k, v in state_dict.items()}
+        dev, dt = self.dev, dtype
+        e = "update_block.encoder"
+        self.convc1 = _PCWeights(sd, e + ".convc1", 15, dev, dt)
+        self.convc2 = _PCWeights(sd, e + ".convc2", 15, dev, dt)
+        self.convf2 = _PCWeights(sd, e + ".convf2", 15, dev, dt)
+        self.conv = _PCWeights(sd, e + ".conv", 15, dev, dt)
+        self.gru = _PCWeights(sd, "update_block.gru", 7, dev, dt)
+        self.fhead = _PCWeights(sd, "update_block.flow_head", 15, dev, dt)
+        self.convf1_w = sd[e + ".convf1_.weight"].to(dev).float().reshape(128, 4).contiguous()
+        self.convf1_b = sd[e + ".convf1_.bias"].to(dev).float().contiguous()
+        self.init_mhs = sd[e + ".init_hidden_state"].to(dev).float().reshape(48).contiguous()
+        self.w_v = sd["update_block.aggregator.to_v.weight"].to(dev).flatten(1).to(dt).contiguous()
+        self.gamma = float(sd["update_block.aggregator.gamma"].reshape(-1)[0])
+        self.w_qk = sd["att.to_qk.weight"].to(dev).flatten(1).to(dt).contiguous()
+        # mask head (stack.py:120-124): conv3x3 128->256 as im2col GEMM with tap-major K, 1x1 256->1152, x100
+        m0 = sd["update_block.mask.0.weight"].to(dev)                       # [256, 128, 3, 3]
+        self.w_m0 = m0.permute(0, 2, 3, 1).reshape(256, 9 * 128).to(dt).contiguous()
+        self.b_m0 = sd["update_block.mask.0.bias"].to(dev).float().contiguous()
+        self.w_m2 = sd["update_block.mask.2.weight"].to(dev).flatten(1).to(dt).contiguous()
+        self.b_m2_x100 = (100.0 * sd["update_block.mask.2.bias"].to(dev).float()).contiguous()
+        enc_dt = encoder_dtype or torch.float32
+        self.fnet = TwinsStage01(sd, "fnet.svt", dev, enc_dt) if "fnet.svt.patch_embeds.0.proj.weight" in sd else None
+        self.cnet = TwinsStage01(sd, "cnet.svt", dev, enc_dt) if "cnet.svt.patch_embeds.0.proj.weight" in sd else None
+        self._ws = {}
+
+    # ------------------------------------------------------------------ buffers
+    def _rows_buf(self, n, c, dtype=None):
+        pitch = _pad8(c)
+        return torch.zeros((n, pitch), dtype=dtype or self.dt, device=self.dev)[:, :c]
+
+    def _workspace(self, Fc, h, w):
+        key = (Fc, h, w)
+        ws = self._ws.get(key)
+        if ws is None:
+            Np = Fc * h * w
+            ws = {
+                "corr2": self._rows_buf(2 * Np, 324),
+                "cor_in": self._rows_buf(Np, 256),
+                "x400": self._rows_buf(Np, 400),
+                "f128": self._rows_buf(Np, 128),
+                "x512": self._rows_buf(Np, 512),
+                "vT": self._rows_buf(128, Np),
+                "delta": self._rows_buf(Np, 4, torch.float32),
+                "sa": self._rows_buf(2 * Np, 512),
+                "sb": self._rows_buf(2 * Np, 512),
+                "hid": self._rows_buf(2 * Np, 768),
+                "qk": self._rows_buf(Np, 256),
+                "attn": torch.empty((Fc, h * w, h * w), dtype=self.dt, device=self.dev),
+                "logits": torch.empty((h * w, h * w), dtype=torch.float32, device=self.dev),
+                "mask": self._rows_buf(Np, 576, torch.float32),
+            }
+            self._ws = {key: ws}      # one shape at a time (volumes dominate memory)
+        return ws
+
+    @staticmethod
+    def _view(buf, n, c):
+        """[n, c] rows view carved from the start of a scratch buffer, pitch = pad8(c)."""
+        base = buf._base if buf._base is not None else buf
+        flat = base.reshape(-1)
+        pitch = _pad8(c)
+        if n * pitch > flat.numel():
+            raise RuntimeError("scratch buffer too small")
+        return flat[: n * pitch].view(n, pitch)[:, :c]
+
+    # ------------------------------------------------------------------ PCBlock
+    def _pcblock(self, x, W, ws, n_img, h, w, outs):
+        """x: rows view [M, Cin].  outs: list of (weight_row_slice, row_slice, out_view, act) for the
+        last 1x1 conv, so that the reference's cat/split around the block costs nothing."""
+        o = self.ops
+        M = x.shape[0]
+        t1 = self._view(ws["hid"], M, W.hid)
+        o.gemm(x, W.w1a, t1, bias=W.b1a, act="gelu")                                         # ffn1.0 + GELU
+        x2 = self._view(ws["sa"], M, W.cin)
+        o.gemm(t1, W.w1b, x2, bias=W.b1b, res=x, act="gelu", dw=(W.dw1_w, W.dw1_b))            # gelu(x+ffn1) ; k=1 dw stage
+        x3 = self._view(ws["sb"], M, W.cin)
+        o.dwconv_res_gelu(x2, x3, n_img, h, w, W.dwk_w, W.dwk_b, W.k)                          # gelu(x + dw_k(x))
+        x4 = self._view(ws["sa"], M, W.cin)
+        o.gemm(x3, W.wpw, x4, bias=W.bpw, res=x3, act="gelu")                                  # gelu(x + pw(x))
+        t2 = self._view(ws["hid"], M, W.hid)
+        o.gemm(x4, W.w2a, t2, bias=W.b2a, act="gelu")                                          # ffn2.0 + GELU
+        for wsl, rsl, out, act in outs:                                                         # ffn2.2
+            o.gemm(t2[rsl], W.w2b[wsl], out, bias=W.b2b[wsl].contiguous(), act=act)
+
+    # ------------------------------------------------------------------ pieces
+    @torch.no_grad()
+    def encode(self, images):
+        """images [1, T, 3, H, W] (raw caller values) -> fmaps [T,256,h,w], net, inp [T-2,128,h,w].
+        network.py:144-170 (the 2*(x/255)-1 normalisation stays inside)."""
+        B, T, _, H, W = images.shape
+        x = 2 * (images.float() / 255.0) - 1.0
+        fmaps = self.fnet(x.reshape(B * T, 3, H, W))
+        cnet = self.cnet(x[:, 1:T - 1].reshape(B * (T - 2), 3, H, W))
+        net, inp = torch.split(cnet, [128, 128], dim=1)
+        return fmaps, torch.tanh(net).contiguous(), torch.relu(inp).contiguous()
+
+    def build_pyramids(self, fmaps):
+        """Forward (frames 1..T-2 vs 2..T-1) and backward (vs 0..T-3) pyramids, network.py:157-158."""
+        T = fmaps.shape[0]
+        c = fmaps[1:T - 1].contiguous()
+        fw = self.ops.corr_volume_pyramid(c, fmaps[2:T].contiguous(), CORR_LEVELS, self.dt)
+        bw = self.ops.corr_volume_pyramid(c, fmaps[0:T - 2].contiguous(), CORR_LEVELS, self.dt)
+        return fw, bw
+
+    def attention(self, ws, Fc, P):
+        """Attention.forward (gma.py:54-76): softmax(q k^T / sqrt(128)) per centre frame."""
+        o = self.ops
+        inp = ws["x512"][:, 128:256]
+        o.gemm(inp, self.w_qk, ws["qk"])
+        for f in range(Fc):
+            q = ws["qk"][f * P:(f + 1) * P, 0:128]
+            k = ws["qk"][f * P:(f + 1) * P, 128:256]
+            o.gemm(q, k, ws["logits"], alpha=128 ** -0.5)
+            o.softmax_rows(ws["logits"], ws["attn"][f])
+
+    def update_step(self, ws, fpyr, bpyr, fc, bc, Fc, h, w):
+        """One iteration of network.py:180-197 (lookups + SKUpdateBlock6..AllDecoder2, stack.py:127-140)."""
+        o = self.ops
+        P = h * w
+        Np = Fc * P
+        corr2, x400, x512 = ws["corr2"], ws["x400"], ws["x512"]
+        o.corr_lookup(fpyr, fc, CORR_RADIUS, out=corr2[:Np])
+        o.corr_lookup(bpyr, bc, CORR_RADIUS, out=corr2[Np:])
+        mf = x512[:, 256:384]
+        o.motion_glue(fc, bc, x400, ws["f128"], mf, self.convf1_w, self.convf1_b, Fc, h, w)
+        full = slice(None)
+        # convc1 on forward and backward correlation (shared weights), gelu(cat) -> cor_in   stack.py:89-92
+        self._pcblock(corr2, self.convc1, ws, 2 * Fc, h, w,
+                      [(full, slice(0, Np), ws["cor_in"][:, 0:128], "gelu"),
+                       (full, slice(Np, 2 * Np), ws["cor_in"][:, 128:256], "gelu")])
+        self._pcblock(ws["cor_in"], self.convc2, ws, Fc, h, w, [(full, full, x400[:, 0:192], None)])
+        self._pcblock(ws["f128"], self.convf2, ws, Fc, h, w, [(full, full, x400[:, 192:256], None)])
+        # conv: 400 -> 172 = 124 motion features + 48 new hidden state                         stack.py:97-102
+        self._pcblock(x400, self.conv, ws, Fc, h, w,
+                      [(slice(0, 124), full, x512[:, 256:380], None),
+                       (slice(124, 172), full, x400[:, 352:400], None)])
+        # Aggregate (gma.py:102-115): mfg = mf + gamma * attn @ to_v(mf)
+        o.gemm(self.w_v, mf, ws["vT"])
+        for f in range(Fc):
+            o.gemm(ws["attn"][f], ws["vT"][:, f * P:(f + 1) * P], x512[f * P:(f + 1) * P, 384:512],
+                   res=mf[f * P:(f + 1) * P], alpha=self.gamma)
+        self._pcblock(x512, self.gru, ws, Fc, h, w, [(full, full, x512[:, 0:128], None)])
+        self._pcblock(x512[:, 0:128], self.fhead, ws, Fc, h, w, [(full, full, ws["delta"], None)])
+        o.coords_add(fc, bc, ws["delta"])
+
+    def mask_rows(self, ws, frames, h, w, chan):
+        """mask head on the rows of `frames` (a slice of centre frames): 100 * mask(net)[:, chan]. stack.py:139"""
+        o = self.ops
+        P = h * w
+        n_img = frames.stop - frames.start
+        rows = slice(frames.start * P, frames.stop * P)
+        net = ws["x512"][rows, 0:128]
+        col = self._view(ws["hid"], n_img * P, 9 * 128)
+        o.im2col3x3(net, col, n_img, h, w)
+        m256 = self._view(ws["sa"], n_img * P, 256)
+        o.gemm(col, self.w_m0, m256, bias=self.b_m0, act="relu")
+        nch = chan.stop - chan.start
+        mask = ws["mask"][: n_img * P, :nch]       # fp32 in both tiers: logits of the 9-tap softmax
+        o.gemm(m256, self.w_m2[chan], mask, bias=self.b_m2_x100[chan].contiguous(), alpha=100.0)
+        return mask
+
+    # ------------------------------------------------------------------ forward
+    @torch.no_grad()
+    def refine(self, fmaps, net, inp, select=None, crop=None, out=None):
+        """fmaps [T,256,h,w], net/inp [T-2,128,h,w] (fp32, CUDA).
+        select=None  -> all flows [1, 2(T-2), 2, 8h, 8w] (forward flows then backward), network.py:210-215
+        select=index -> only that flow [2, out_h, out_w]; crop=(top, left, out_h, out_w) fuses the unpad."""
+        o = self.ops
+        T, _, h, w = fmaps.shape
+        Fc, P = T - 2, h * w
+        ws = self._workspace(Fc, h, w)
+        fpyr, bpyr = self.build_pyramids(fmaps.float())
+        x512 = ws["x512"]
+        o.nchw_to_rows(net.float().contiguous(), x512[:, 0:128])
+        o.nchw_to_rows(inp.float().contiguous(), x512[:, 128:256])
+        o.rows_fill(ws["x400"][:, 352:400], self.init_mhs)          # init_hidden_state, stack.py:72-73
+        self.attention(ws, Fc, P)
+        fc = o.coords_grid(Fc, h, w, self.dev)
+        bc = o.coords_grid(Fc, h, w, self.dev)
+        for _ in range(self.iters):
+            self.update_step(ws, fpyr, bpyr, fc, bc, Fc, h, w)
+        del fpyr, bpyr
+        if select is None:
+            flows = torch.empty((1, 2 * Fc, 2, 8 * h, 8 * w), dtype=torch.float32, device=self.dev)
+            mk = self.mask_rows(ws, slice(0, Fc), h, w, slice(0, 576))
+            o.convex_upsample8(fc, mk, out=flows[0, :Fc], flow_is_coords=True)
+            mk = self.mask_rows(ws, slice(0, Fc), h, w, slice(576, 1152))
+            o.convex_upsample8(bc, mk, out=flows[0, Fc:], flow_is_coords=True)
+            return flows
+        direction, frame = divmod(select, Fc)
+        coords = (fc, bc)[direction][frame:frame + 1]
+        mk = self.mask_rows(ws, slice(frame, frame + 1), h, w, slice(576 * direction, 576 * (direction + 1)))
+        if out is None:
+            oh, ow = (crop[2], crop[3]) if crop else (8 * h, 8 * w)
+            out = torch.empty((2, oh, ow), dtype=torch.float32, device=self.dev)
+        o.convex_upsample8(coords.contiguous(), mk, out=out[None], crop=crop, flow_is_coords=True)
+        return out
+
+    @torch.no_grad()
+    def forward(self, images, select=None, crop=None):
+        fmaps, net, inp = self.encode(images)
+        return self.refine(fmaps, net, inp, select=select, crop=crop)

@@ -1,0 +1,333 @@
+"""Tensor-level wrappers over the C ABI (include/vfml.h).  torch is used for device memory and
+streams only; every function launches libvfml kernels on the current CUDA stream.
+
+"rows views": 2-D tensors [n_rows, n_cols] with stride(1) == 1 (column slices of a wider
+[n_rows, pitch] buffer are fine); their row stride is the pitch handed to the kernels.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import F16, F32, NCHW, ROWS
+
+_DT = {torch.float32: F32, torch.float16: F16}
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise ValueError("libvfml operates on CUDA tensors only (no CPU fallback)")
+
+
+def _p(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _dt(t):
+    try:
+        return _DT[t.dtype]
+    except KeyError:
+        raise ValueError(f"unsupported dtype {t.dtype}") from None
+
+
+def _rows(t, name):
+    if t.dim() != 2 or (t.shape[1] > 1 and t.stride(1) != 1):
+        raise ValueError(f"{name}: expected a rows view [n, c] with unit column stride, got {tuple(t.shape)} / {t.stride()}")
+    return t
+
+
+def _f32c(t, name):
+    if t.dtype != torch.float32 or not t.is_contiguous():
+        raise ValueError(f"{name}: expected a contiguous float32 tensor")
+    return t
+
+
+# ------------------------------------------------------------------ layout
+def nchw_to_rows(src, dst):
+    """src [n, c, h, w] fp32 -> dst rows view [n*h*w, c]."""
+    _cuda(src, dst)
+    _f32c(src, "src"); _rows(dst, "dst")
+    n, c, h, w = src.shape
+    if dst.shape != (n * h * w, c):
+        raise ValueError("nchw_to_rows: shape mismatch")
+    _lib.check(_lib.load().vfml_nchw_to_rows(_p(src), _p(dst), n, c, h * w, dst.stride(0), 0, _dt(dst), _stream()), "nchw_to_rows")
+    return dst
+
+
+def rows_to_nchw(src, dst):
+    """src rows view [n*h*w, c] -> dst [n, c, h, w] fp32."""
+    _cuda(src, dst)
+    _rows(src, "src"); _f32c(dst, "dst")
+    n, c, h, w = dst.shape
+    if src.shape != (n * h * w, c):
+        raise ValueError("rows_to_nchw: shape mismatch")
+    _lib.check(_lib.load().vfml_rows_to_nchw(_p(src), _p(dst), n, c, h * w, src.stride(0), 0, _dt(src), _stream()), "rows_to_nchw")
+    return dst
+
+
+# ------------------------------------------------------------------ correlation
+def pyramid_shapes(h, w, num_levels):
+    out = []
+    for _ in range(num_levels):
+        out.append((h, w))
+        h, w = h // 2, w // 2
+    return out
+
+
+def corr_volume_pyramid(fmap1, fmap2, num_levels=4, vol_dtype=torch.float32):
+    """-> list of level tensors [n*h*w, 1, h_l, w_l] (the reference's CorrBlock.corr_pyramid)."""
+    _cuda(fmap1, fmap2)
+    _f32c(fmap1, "fmap1"); _f32c(fmap2, "fmap2")
+    if fmap1.shape != fmap2.shape or fmap1.dim() != 4:
+        raise ValueError("corr_volume_pyramid: fmaps must be [n, C, h, w] of equal shape")
+    n, Cc, h, w = fmap1.shape
+    levels = [torch.empty((n * h * w, 1, hl, wl), dtype=vol_dtype, device=fmap1.device)
+              for hl, wl in pyramid_shapes(h, w, num_levels)]
+    if any(l.numel() == 0 for l in levels) and n > 0:
+        raise ValueError(f"corr_volume_pyramid: {h}x{w} is too small for {num_levels} levels")
+    arr = (C.c_void_p * num_levels)(*[l.data_ptr() for l in levels])
+    lib = _lib.load()
+    ws_bytes = lib.vfml_corr_volume_workspace(n, Cc, h, w, _DT[vol_dtype])
+    ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=fmap1.device)
+    _lib.check(lib.vfml_corr_volume_pyramid(_p(fmap1), _p(fmap2), n, Cc, h, w, arr, num_levels, _DT[vol_dtype],
+                                            _p(ws), ws_bytes, _stream()), "corr_volume_pyramid")
+    return levels
+
+
+def corr_lookup(levels, coords, radius=4, out=None, out_dtype=torch.float32):
+    """coords [n, 2, h, w] fp32.  out=None -> new NCHW [n, L*(2r+1)^2, h, w];
+    out = rows view [n*h*w, L*(2r+1)^2] -> written in rows layout."""
+    _cuda(coords, *levels)
+    _f32c(coords, "coords")
+    n, two, h, w = coords.shape
+    L = len(levels)
+    ch = L * (2 * radius + 1) ** 2
+    if two != 2 or levels[0].shape[0] != n * h * w or tuple(levels[0].shape[-2:]) != (h, w):
+        raise ValueError("corr_lookup: coords do not match the pyramid")
+    arr = (C.c_void_p * L)(*[l.data_ptr() for l in levels])
+    if out is None:
+        out = torch.empty((n, ch, h, w), dtype=out_dtype, device=coords.device)
+        layout, pitch = NCHW, 0
+    else:
+        _rows(out, "out")
+        if out.shape != (n * h * w, ch):
+            raise ValueError("corr_lookup: out must be [n*h*w, L*(2r+1)^2]")
+        layout, pitch = ROWS, out.stride(0)
+    _lib.check(_lib.load().vfml_corr_lookup(arr, L, _dt(levels[0]), n, h, w, radius, _p(coords), _p(out), layout, pitch, 0,
+                                            _dt(out), _stream()), "corr_lookup")
+    return out
+
+
+def convex_upsample8(flow, mask, out=None, crop=None, flow_is_coords=False):
+    """flow [n, 2, h, w] fp32; mask [n, 576, h, w] fp32 or rows view [n*h*w, 576].
+    crop=(top, left, out_h, out_w) selects a window of the 8h x 8w result (unpad fused);
+    out: fp32 tensor view [n, 2, out_h, out_w] with unit x stride (may be a slice of a larger frame)."""
+    _cuda(flow, mask)
+    _f32c(flow, "flow")
+    n, _, h, w = flow.shape
+    top, left, oh, ow = crop if crop is not None else (0, 0, 8 * h, 8 * w)
+    if out is None:
+        out = torch.empty((n, 2, oh, ow), dtype=torch.float32, device=flow.device)
+    if out.dtype != torch.float32 or out.shape != (n, 2, oh, ow) or (ow > 1 and out.stride(3) != 1):
+        raise ValueError("convex_upsample8: bad out tensor")
+    if mask.dim() == 4:
+        _f32c(mask, "mask")
+        if mask.shape != (n, 576, h, w):
+            raise ValueError("convex_upsample8: mask must be [n, 576, h, w]")
+        layout, pitch = NCHW, 0
+    else:
+        _rows(mask, "mask")
+        if mask.shape != (n * h * w, 576):
+            raise ValueError("convex_upsample8: mask rows must be [n*h*w, 576]")
+        layout, pitch = ROWS, mask.stride(0)
+    _lib.check(_lib.load().vfml_convex_upsample8(_p(flow), _p(mask), layout, pitch, 0, _dt(mask), n, h, w, _p(out),
+                                                 out.stride(0), out.stride(1), out.stride(2), top, left, oh, ow,
+                                                 int(flow_is_coords), _stream()), "convex_upsample8")
+    return out
+
+
+# ------------------------------------------------------------------ post-pass
+def encode_gamedev(flow, width, height, scale=200.0, clamp=20.0):
+    """flow [H, W, 2] fp32 CUDA -> [H, W, 3] u8 CUDA."""
+    _cuda(flow)
+    _f32c(flow, "flow")
+    H, W, _ = flow.shape
+    out = torch.empty((H, W, 3), dtype=torch.uint8, device=flow.device)
+    _lib.check(_lib.load().vfml_encode_gamedev(_p(flow), _p(out), H, W, float(width), float(height), float(scale),
+                                               float(clamp), _stream()), "encode_gamedev")
+    return out
+
+
+def encode_mv_rg8(flow, clamp=64.0):
+    _cuda(flow)
+    _f32c(flow, "flow")
+    H, W, _ = flow.shape
+    out = torch.empty((H, W, 3), dtype=torch.uint8, device=flow.device)
+    _lib.check(_lib.load().vfml_encode_mv_rg8(_p(flow), _p(out), H, W, float(clamp), _stream()), "encode_mv_rg8")
+    return out
+
+
+def decode_mv_rg8(rgb, clamp=64.0):
+    _cuda(rgb)
+    if rgb.dtype != torch.uint8 or not rgb.is_contiguous():
+        raise ValueError("decode_mv_rg8: expected contiguous uint8")
+    H, W, _ = rgb.shape
+    out = torch.empty((H, W, 2), dtype=torch.float32, device=rgb.device)
+    _lib.check(_lib.load().vfml_decode_mv_rg8(_p(rgb), _p(out), H, W, float(clamp), _stream()), "decode_mv_rg8")
+    return out
+
+
+def taa_init(cur):
+    _cuda(cur)
+    H, W, _ = cur.shape
+    out = torch.empty((H, W, 3), dtype=torch.float64, device=cur.device)
+    _lib.check(_lib.load().vfml_taa_init(_p(cur), _p(out), H, W, _stream()), "taa_init")
+    return out
+
+
+def taa(cur, flow, history, alpha, sigma_color, mode, hist_f32):
+    """cur [H,W,3] u8, flow [H,W,2] fp32 or None, history [H,W,3] f64 -> new [H,W,3] f64."""
+    _cuda(cur, flow, history)
+    H, W, _ = cur.shape
+    if cur.dtype != torch.uint8 or history.dtype != torch.float64 or history.shape != cur.shape:
+        raise ValueError("taa: bad tensor types")
+    if flow is not None:
+        _f32c(flow, "flow")
+    out = torch.empty_like(history)
+    _lib.check(_lib.load().vfml_taa(_p(cur.contiguous()), _p(flow), _p(history.contiguous()), _p(out), H, W, float(alpha),
+                                    float(sigma_color), int(mode), int(bool(hist_f32)), _stream()), "taa")
+    return out
+
+
+# ------------------------------------------------------------------ update-step building blocks
+def gemm(a, w, out, bias=None, res=None, act=None, dw=None, alpha=1.0, addto=False):
+    """out[m, n] = epi(alpha * sum_k a[m, k] w[n, k]).  a, w, out, res: rows views."""
+    _cuda(a, w, out, bias, res)
+    _rows(a, "a"); _rows(w, "w"); _rows(out, "out")
+    M, K = a.shape
+    N = w.shape[0]
+    if w.shape[1] != K or out.shape != (M, N) or a.dtype != w.dtype:
+        raise ValueError(f"gemm: shape/dtype mismatch a{tuple(a.shape)} w{tuple(w.shape)} out{tuple(out.shape)}")
+    d = _lib.GemmDesc()
+    d.A, d.B, d.D = a.data_ptr(), w.data_ptr(), out.data_ptr()
+    d.lda, d.ldb, d.ldd = a.stride(0), w.stride(0), out.stride(0)
+    d.M, d.N, d.K, d.batch = M, N, K, 1
+    d.alpha = alpha
+    epi = 0
+    if bias is not None:
+        _f32c(bias, "bias")
+        d.bias = bias.data_ptr(); epi |= _lib.EPI_BIAS
+    if res is not None:
+        _rows(res, "res")
+        if res.shape != (M, N) or res.dtype != a.dtype:
+            raise ValueError("gemm: residual mismatch")
+        d.res = res.data_ptr(); d.ldr = res.stride(0); epi |= _lib.EPI_RES
+    if act == "gelu":
+        epi |= _lib.EPI_GELU
+    elif act == "relu":
+        epi |= _lib.EPI_RELU
+    elif act is not None:
+        raise ValueError(f"gemm: unknown activation {act}")
+    if dw is not None:
+        d.dw_w, d.dw_b = _f32c(dw[0], "dw_w").data_ptr(), _f32c(dw[1], "dw_b").data_ptr()
+        epi |= _lib.EPI_DW1
+    if addto:
+        epi |= _lib.EPI_ADDTO
+    d.epi = epi
+    d.in_dtype, d.out_dtype = _dt(a), _dt(out)
+    _lib.check(_lib.load().vfml_gemm(C.byref(d), _stream()), "gemm")
+    return out
+
+
+def gemm_batched(a, b, out, alpha=1.0):
+    """out[i] = alpha * a[i] @ b[i]^T for 3-D views [batch, rows, k] with unit k stride."""
+    _cuda(a, b, out)
+    Bn, M, K = a.shape
+    N = b.shape[1]
+    if b.shape != (Bn, N, K) or out.shape != (Bn, M, N) or a.stride(2) != 1 or b.stride(2) != 1 or out.stride(2) != 1:
+        raise ValueError("gemm_batched: shape mismatch")
+    d = _lib.GemmDesc()
+    d.A, d.B, d.D = a.data_ptr(), b.data_ptr(), out.data_ptr()
+    d.lda, d.ldb, d.ldd = a.stride(1), b.stride(1), out.stride(1)
+    d.strideA, d.strideB, d.strideD = a.stride(0), b.stride(0), out.stride(0)
+    d.M, d.N, d.K, d.batch = M, N, K, Bn
+    d.alpha = alpha
+    d.in_dtype, d.out_dtype = _dt(a), _dt(out)
+    _lib.check(_lib.load().vfml_gemm(C.byref(d), _stream()), "gemm_batched")
+    return out
+
+
+def dwconv_res_gelu(x, y, n_img, h, w, weight_tapmajor, bias, k):
+    """y = gelu(x + dwconv_k(x) + b) over rows views [n_img*h*w, C]; weight [k*k, C] fp32."""
+    _cuda(x, y, weight_tapmajor, bias)
+    _rows(x, "x"); _rows(y, "y")
+    Cc = x.shape[1]
+    if x.shape != y.shape or x.shape[0] != n_img * h * w or weight_tapmajor.shape != (k * k, Cc) or x.dtype != y.dtype:
+        raise ValueError("dwconv_res_gelu: shape mismatch")
+    _lib.check(_lib.load().vfml_dwconv_res_gelu(_p(x), _p(y), n_img, h, w, Cc, x.stride(0), y.stride(0),
+                                                _p(_f32c(weight_tapmajor, "w")), _p(_f32c(bias, "b")), k, _dt(x), _stream()),
+               "dwconv_res_gelu")
+    return y
+
+
+def softmax_rows(src, dst):
+    _cuda(src, dst)
+    _rows(src, "src"); _rows(dst, "dst")
+    if src.dtype != torch.float32 or src.shape != dst.shape:
+        raise ValueError("softmax_rows: src must be fp32 and match dst")
+    _lib.check(_lib.load().vfml_softmax_rows(_p(src), _p(dst), src.shape[0], src.shape[1], src.stride(0), dst.stride(0),
+                                             _dt(dst), _stream()), "softmax_rows")
+    return dst
+
+
+def motion_glue(fcoords, bcoords, x400, f128, mf, w1, b1, n_frames, h, w):
+    _cuda(fcoords, bcoords, x400, f128, mf, w1, b1)
+    _rows(x400, "x400"); _rows(f128, "f128"); _rows(mf, "mf")
+    rows = n_frames * h * w
+    if x400.shape != (rows, 400) or f128.shape != (rows, 128) or mf.shape != (rows, 128):
+        raise ValueError("motion_glue: shape mismatch")
+    if not (x400.dtype == f128.dtype == mf.dtype):
+        raise ValueError("motion_glue: dtype mismatch")
+    _lib.check(_lib.load().vfml_motion_glue(_p(_f32c(fcoords, "fc")), _p(_f32c(bcoords, "bc")), _p(x400), x400.stride(0),
+                                            _p(f128), f128.stride(0), _p(mf), mf.stride(0), 0, _p(_f32c(w1, "w1")),
+                                            _p(_f32c(b1, "b1")), n_frames, h, w, _dt(x400), _stream()), "motion_glue")
+
+
+def coords_add(fcoords, bcoords, delta):
+    _cuda(fcoords, bcoords, delta)
+    _rows(delta, "delta")
+    n, _, h, w = fcoords.shape
+    if delta.dtype != torch.float32 or delta.shape != (n * h * w, 4):
+        raise ValueError("coords_add: delta must be fp32 [n*h*w, 4]")
+    _lib.check(_lib.load().vfml_coords_add(_p(_f32c(fcoords, "fc")), _p(_f32c(bcoords, "bc")), _p(delta), delta.stride(0),
+                                           n, h * w, _stream()), "coords_add")
+
+
+def coords_grid(n, h, w, device):
+    out = torch.empty((n, 2, h, w), dtype=torch.float32, device=device)
+    _cuda(out)
+    _lib.check(_lib.load().vfml_coords_grid(_p(out), n, h, w, _stream()), "coords_grid")
+    return out
+
+
+def rows_fill(view, values):
+    _cuda(view, values)
+    _rows(view, "view")
+    _lib.check(_lib.load().vfml_rows_fill(_p(view), view.stride(0), 0, view.shape[1], view.shape[0],
+                                          _p(_f32c(values, "values")), _dt(view), _stream()), "rows_fill")
+
+
+def im2col3x3(x, out, n_img, h, w):
+    _cuda(x, out)
+    _rows(x, "x"); _rows(out, "out")
+    Cc = x.shape[1]
+    if out.shape != (x.shape[0], 9 * Cc) or x.dtype != out.dtype:
+        raise ValueError("im2col3x3: shape mismatch")
+    _lib.check(_lib.load().vfml_im2col3x3(_p(x), _p(out), n_img, h, w, Cc, x.stride(0), out.stride(0), _dt(x), _stream()),
+               "im2col3x3")
+    return out

@@ -1,0 +1,146 @@
+"""VideoFlowCore on libvfml kernels.  Mirrors processing/videoflow_core.py:33-242 of the reference:
+same constructor, methods, checkpoint naming, return values and exceptions."""
+import os
+
+import torch
+
+from ..mof import MOFEngine
+
+_PRECISIONS = {"fp32": torch.float32, "fp16": torch.float16}
+
+
+def pad_amounts(ht, wd, mode="sintel"):
+    """InputPadder (VideoFlow/core/utils/utils.py:9-18): (left, right, top, bottom) to a multiple of 8."""
+    ph = (((ht // 8) + 1) * 8 - ht) % 8
+    pw = (((wd // 8) + 1) * 8 - wd) % 8
+    if mode == "sintel":
+        return pw // 2, pw - pw // 2, ph // 2, ph - ph // 2
+    return pw // 2, pw - pw // 2, 0, ph
+
+
+class _Config(dict):
+    """Minimal attribute + item config (the reference uses a yacs CfgNode)."""
+    __getattr__ = dict.get
+
+    def __setattr__(self, k, v):
+        self[k] = v
+
+
+class VideoFlowCore:
+    def __init__(self, device, fast_mode=False, dataset='sintel', architecture='mof', variant='standard',
+                 precision=None):
+        self.device = device
+        self.fast_mode = fast_mode
+        self.dataset = dataset
+        self.architecture = architecture.lower()
+        self.variant = variant
+        self.precision = precision or os.environ.get("VFML_PRECISION", "fp32")
+        if self.precision not in _PRECISIONS:
+            raise ValueError(f"precision must be one of {sorted(_PRECISIONS)}, got {self.precision}")
+        self.model = None
+        self.cfg = None
+
+    # ------------------------------------------------------------------ loading
+    def _model_path(self):
+        arch_upper = self.architecture.upper()
+        if self.variant == 'noise' and self.dataset == 'things':
+            return f"VideoFlow_ckpt/{arch_upper}_{self.dataset}_288960noise.pth"
+        return f"VideoFlow_ckpt/{arch_upper}_{self.dataset}.pth"
+
+    def _make_cfg(self, model_path):
+        # VideoFlow/configs/multiframes_sintel_submission.py:16-37 (the values the network is built from)
+        cfg = _Config(model=model_path, network="MOFNetStack", decoder_depth=32, corr_levels=4, corr_radius=4,
+                      mixed_precision=self.precision == "fp16", feat_dim=256, down_ratio=8)
+        if self.fast_mode:   # written on the top-level cfg only; the network ignores them
+            cfg.decoder_depth, cfg.corr_levels, cfg.corr_radius = 6, 3, 3
+        return cfg
+
+    def load_model(self):
+        model_path = self._model_path()
+        if not os.path.exists(model_path):
+            raise FileNotFoundError(f"VideoFlow model weights not found: {model_path}")
+        checkpoint = torch.load(model_path, map_location="cpu")
+        self.load_state_dict(checkpoint, model_path)
+        print(f"[Model] VideoFlow model loaded successfully:")
+        print(f"  Path: {model_path}")
+        print(f"  Architecture: {self.architecture.upper()} ({self.architecture})")
+        print(f"  Dataset: {self.dataset}")
+        print(f"  Variant: {self.variant}")
+        print(f"  Device: {self.device}")
+        return model_path
+
+    def load_state_dict(self, state_dict, model_path="<state_dict>", iters=32):
+        """Build the engine from an in-memory checkpoint (upstream key names, optional 'module.' prefix)."""
+        if self.architecture != 'mof':
+            raise NotImplementedError("only the MOF architecture is implemented in this build")
+        if not str(self.device).startswith("cuda"):
+            raise RuntimeError("this build runs on CUDA devices only (no CPU fallback)")
+        self.cfg = self._make_cfg(model_path)
+        self.model = MOFEngine(state_dict, self.device, _PRECISIONS[self.precision], iters=iters,
+                               encoder_dtype=_PRECISIONS[self.precision] if self.precision == "fp16" else None)
+
+    # ------------------------------------------------------------------ inference
+    def _validate(self, t):
+        if self.model is None:
+            raise RuntimeError("VideoFlow model not loaded. Call load_model() first.")
+        if not isinstance(t, torch.Tensor):
+            raise ValueError("Input must be a torch.Tensor")
+        td, md = str(t.device), str(self.device)
+        if not ((td.startswith('cuda') and md == 'cuda') or (md.startswith('cuda') and td == 'cuda') or td == md):
+            raise ValueError(f"Input tensor device ({t.device}) doesn't match model device ({self.device})")
+        if len(t.shape) != 5:
+            raise ValueError(f"Input tensor must have 5 dimensions [B,T,C,H,W], got {len(t.shape)}")
+        if t.shape[0] != 1:
+            raise ValueError(f"Batch size must be 1, got {t.shape[0]}")
+        if t.shape[2] != 3:
+            raise ValueError(f"Must have 3 color channels, got {t.shape[2]}")
+
+    def compute_flow_from_tensor(self, frame_batch_tensor, out=None):
+        """[1, T, 3, H, W] -> [2, H, W]: replicate-pad to x8 ('sintel' mode), forward, unpad, flow index T-2
+        (the first backward flow).  Only that flow is upsampled; the unpad is fused into the
+        upsampling kernel's cropped write."""
+        self._validate(frame_batch_tensor)
+        H, W = frame_batch_tensor.shape[-2:]
+        l, r, t, b = pad_amounts(H, W)
+        x = frame_batch_tensor
+        if l or r or t or b:
+            x = torch.nn.functional.pad(x, [l, r, t, b, 0, 0], mode='replicate')
+        Tn = x.shape[1]
+        with torch.no_grad():
+            fmaps, net, inp = self.model.encode(x)
+            return self.model.refine(fmaps, net, inp, select=Tn - 2, crop=(t, l, H, W), out=out)
+
+    def is_model_loaded(self):
+        return self.model is not None
+
+    def get_model_info(self):
+        if self.model is None:
+            return {"status": "not_loaded"}
+        return {
+            "status": "loaded",
+            "model_path": getattr(self.cfg, 'model', 'unknown') if self.cfg else 'unknown',
+            "dataset": self.dataset,
+            "architecture": self.architecture.upper(),
+            "variant": self.variant,
+            "config": {
+                "decoder_depth": getattr(self.cfg, 'decoder_depth', 'default'),
+                "corr_levels": getattr(self.cfg, 'corr_levels', 'default'),
+                "corr_radius": getattr(self.cfg, 'corr_radius', 'default'),
+            },
+            "fast_mode": self.fast_mode,
+            "device": str(self.device),
+        }
+
+    def get_device(self):
+        return self.device
+
+    def set_eval_mode(self):
+        pass   # the engine is inference-only
+
+    def get_memory_usage(self):
+        dev = torch.device(self.device)
+        if dev.type == 'cuda':
+            return {"allocated": torch.cuda.memory_allocated(dev) / 1024**2,
+                    "cached": torch.cuda.memory_reserved(dev) / 1024**2,
+                    "max_allocated": torch.cuda.max_memory_allocated(dev) / 1024**2}
+        return {"message": "Memory tracking only available for CUDA devices"}

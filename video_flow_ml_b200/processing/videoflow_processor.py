@@ -1,0 +1,160 @@
+"""VideoFlowProcessor on libvfml kernels.  Mirrors processing/videoflow_processor.py:20-361 of the
+reference (window choice, tile grid, progress-bar calls, validation, return types)."""
+import numpy as np
+import torch
+
+from .videoflow_core import VideoFlowCore
+
+
+class VideoFlowProcessor:
+    def __init__(self, device, fast_mode=False, tile_mode=False, sequence_length=5,
+                 dataset='sintel', architecture='mof', variant='standard', precision=None):
+        self.device = device
+        self.fast_mode = fast_mode
+        self.tile_mode = tile_mode
+        self.sequence_length = sequence_length
+        self.dataset = dataset
+        self.architecture = architecture
+        self.variant = variant
+        self.core = VideoFlowCore(device, fast_mode, dataset, architecture, variant, precision=precision)
+
+    def load_model(self):
+        model_path = self.core.load_model()
+        print(f"VideoFlow model loaded successfully from: {model_path}")
+
+    # ------------------------------------------------------------------ host logic
+    def calculate_tile_grid(self, width, height, tile_size=1280):
+        """Disjoint fixed-size tiles, ragged at the right / bottom edges (reference :73-110)."""
+        cols = -(-width // tile_size)
+        rows = -(-height // tile_size)
+        tiles_info = [{'x': c * tile_size, 'y': r * tile_size,
+                       'width': min(tile_size, width - c * tile_size), 'height': min(tile_size, height - r * tile_size),
+                       'col': c, 'row': r} for r in range(rows) for c in range(cols)]
+        return tile_size, tile_size, cols, rows, tiles_info
+
+    def extract_tile(self, frame, tile_info):
+        x, y, w, h = tile_info['x'], tile_info['y'], tile_info['width'], tile_info['height']
+        return frame[y:y + h, x:x + w]
+
+    def window_indices(self, n_frames, frame_idx):
+        """Centred window clipped to the clip; short windows repeat the first frame when clipped at the
+        start, otherwise the last (reference :134-150)."""
+        half = self.sequence_length // 2
+        start = max(0, frame_idx - half)
+        ids = list(range(start, min(n_frames, frame_idx + half + 1)))
+        while len(ids) < self.sequence_length:
+            if start == 0:
+                ids.insert(0, ids[0])
+            else:
+                ids.append(ids[-1])
+        return ids[:self.sequence_length]
+
+    def prepare_frame_sequence(self, frames, frame_idx):
+        """-> [1, T, 3, H, W] fp32 on the device; uint8 frames are scaled to [0, 1], float frames pass
+        through (reference :152-162)."""
+        ids = self.window_indices(len(frames), frame_idx)
+        seq = [frames[i] for i in ids]
+        if all(f.dtype == np.uint8 for f in seq):
+            # one u8 upload, conversion on the device (same fp32 division as the reference's numpy one)
+            u8 = torch.from_numpy(np.stack(seq)).to(self.device, non_blocking=True)
+            return (u8.permute(0, 3, 1, 2).float() / 255.0).unsqueeze(0)
+        tensors = [torch.from_numpy((f.astype(np.float32) / 255.0) if f.dtype == np.uint8 else f.astype(np.float32)).permute(2, 0, 1)
+                   for f in seq]
+        return torch.stack(tensors).unsqueeze(0).to(self.device)
+
+    # ------------------------------------------------------------------ inference
+    def compute_optical_flow(self, frames, frame_idx):
+        if not self.core.is_model_loaded():
+            raise RuntimeError("Model not loaded. Call load_model() first.")
+        flow = self.core.compute_flow_from_tensor(self.prepare_frame_sequence(frames, frame_idx))
+        return flow.permute(1, 2, 0).cpu().numpy()
+
+    def compute_optical_flow_with_progress(self, frames, frame_idx, tile_pbar=None):
+        if not self.core.is_model_loaded():
+            raise RuntimeError("Model not loaded. Call load_model() first.")
+        if tile_pbar is not None:
+            tile_pbar.set_description("Preparing frames")
+            tile_pbar.reset()
+        batch = self.prepare_frame_sequence(frames, frame_idx)
+        if tile_pbar is not None:
+            tile_pbar.set_description("Running VideoFlow")
+            tile_pbar.update(2)
+        flow = self.core.compute_flow_from_tensor(batch)
+        if tile_pbar is not None:
+            tile_pbar.set_description("Processing output")
+            tile_pbar.update(1)
+        flow_np = flow.permute(1, 2, 0).cpu().numpy()
+        if tile_pbar is not None:
+            tile_pbar.set_description("Completed")
+            tile_pbar.update(1)
+        return flow_np
+
+    def compute_optical_flow_tiled(self, frames, frame_idx, tile_pbar=None, overall_pbar=None):
+        """Disjoint 1280x1280 tiles, each an independent clip, pasted without blending (reference :231-283).
+        Tiles are cropped from the window's frames only and each tile's flow is written by the upsampling
+        kernel straight into the full-frame device buffer (no per-tile D2H, no host paste)."""
+        if not self.tile_mode:
+            return self.compute_optical_flow(frames, frame_idx)
+        if not self.core.is_model_loaded():
+            raise RuntimeError("Model not loaded. Call load_model() first.")
+        height, width = frames[frame_idx].shape[:2]
+        _, _, _, _, tiles_info = self.calculate_tile_grid(width, height)
+        full = torch.zeros((2, height, width), dtype=torch.float32, device=self.device)
+        window = self.prepare_frame_sequence(frames, frame_idx)
+        for i, ti in enumerate(tiles_info):
+            if overall_pbar is not None:
+                overall_pbar.set_description(f"Tile {i+1}/{len(tiles_info)} ({ti['width']}x{ti['height']})")
+            if tile_pbar is not None:
+                tile_pbar.set_description("Running VideoFlow")
+                tile_pbar.reset()
+            x, y, w, h = ti['x'], ti['y'], ti['width'], ti['height']
+            tile = window[..., y:y + h, x:x + w].contiguous()
+            self.core.compute_flow_from_tensor(tile, out=full[:, y:y + h, x:x + w])
+            if tile_pbar is not None:
+                tile_pbar.set_description("Completed")
+                tile_pbar.update(4)
+            if overall_pbar is not None:
+                overall_pbar.update(1)
+        return full.permute(1, 2, 0).cpu().numpy()
+
+    # ------------------------------------------------------------------ misc API
+    def is_model_loaded(self):
+        return self.core.is_model_loaded()
+
+    def get_model_info(self):
+        info = self.core.get_model_info()
+        if info["status"] == "loaded":
+            info.update({"tile_mode": self.tile_mode, "sequence_length": self.sequence_length,
+                         "processor_type": "VideoFlowProcessor"})
+        return info
+
+    def get_memory_usage(self):
+        return self.core.get_memory_usage()
+
+    def validate_frames(self, frames, frame_idx):
+        if not isinstance(frames, list):
+            raise ValueError("Frames must be a list of numpy arrays")
+        if len(frames) == 0:
+            raise ValueError("Frames list cannot be empty")
+        if frame_idx < 0 or frame_idx >= len(frames):
+            raise ValueError(f"Frame index {frame_idx} out of range [0, {len(frames)-1}]")
+        f = frames[0]
+        if not isinstance(f, np.ndarray):
+            raise ValueError("Frames must be numpy arrays")
+        if len(f.shape) != 3:
+            raise ValueError(f"Frames must be 3D arrays [H,W,C], got shape {f.shape}")
+        if f.shape[2] != 3:
+            raise ValueError(f"Frames must have 3 color channels, got {f.shape[2]}")
+        if f.dtype not in [np.uint8, np.float32, np.float64]:
+            raise ValueError(f"Unsupported frame dtype: {f.dtype}")
+        if f.dtype != np.uint8 and (f.max() > 1.0 or f.min() < 0.0):
+            if not (f.max() <= 255.0 and f.min() >= 0.0):
+                raise ValueError("Float frames must be in range [0.0, 1.0] or [0.0, 255.0]")
+
+    def set_tile_mode(self, enabled):
+        self.tile_mode = enabled
+
+    def set_sequence_length(self, length):
+        if length < 1 or length > 10:
+            raise ValueError("Sequence length must be between 1 and 10")
+        self.sequence_length = length
