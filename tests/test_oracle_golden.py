@@ -95,6 +95,14 @@ def test_mof_end_to_end_wrapper(golden, mof_weights):
     assert np.sqrt(((f0 - g["flow_u8_0"]) ** 2).sum(-1)).max() < 1e-2
 
 
+def test_mof_end_to_end_wellconditioned(golden):
+    """Second weight set (gain 1.0, make_golden_wellcond.py): the fixture the GPU tiers are held to."""
+    g = golden("mof_e2e_g10.npz")
+    sd = mof.mof_synthetic_weights(0, gain=1.0)
+    f2 = mof.core_compute_flow(mof.frames_to_window(cases.mof_case(), 2, 5), sd).permute(1, 2, 0).numpy()
+    assert np.sqrt(((f2 - g["flow_2"]) ** 2).sum(-1)).max() < 1e-3
+
+
 def test_host_logic(golden):
     with open(os.path.join(os.path.dirname(cases.__file__), "host.json")) as f:
         host = json.load(f)

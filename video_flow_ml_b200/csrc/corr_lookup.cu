@@ -217,7 +217,6 @@ using namespace vfml;
 extern "C" int vfml_corr_lookup(const void* const* levels, int num_levels, int vol_dtype, int n_frames,
                                 int h, int w, int radius, const float* coords, void* out, int out_layout,
                                 int out_pitch, int out_col, int out_dtype, vfml_stream_t s) {
-    VFML_REQUIRE(levels && coords && out, "corr_lookup: null pointer");
     VFML_REQUIRE(num_levels >= 1 && num_levels <= LK_MAXL, "corr_lookup: num_levels %d not in 1..4", num_levels);
     VFML_REQUIRE(radius >= 0 && radius <= 8, "corr_lookup: radius %d not in 0..8", radius);
     VFML_REQUIRE(n_frames >= 0 && h > 0 && w > 0, "corr_lookup: bad shape");
@@ -227,6 +226,7 @@ extern "C" int vfml_corr_lookup(const void* const* levels, int num_levels, int v
     if (out_layout == VFML_ROWS)
         VFML_REQUIRE(out_pitch >= out_col + CH && out_col >= 0, "corr_lookup: pitch %d < col %d + %d", out_pitch, out_col, CH);
     if (n_frames == 0) return VFML_OK;
+    VFML_REQUIRE(levels && coords && out, "corr_lookup: null pointer");
     LookupParams p{};
     int lh = h, lw = w;
     for (int l = 0; l < num_levels; ++l) {

@@ -139,8 +139,9 @@ extern "C" int vfml_corr_volume_pyramid(const float* fmap1, const float* fmap2, 
                                         void* const* levels, int num_levels, int vol_dtype, void* workspace,
                                         size_t workspace_bytes, vfml_stream_t s) {
     (void)workspace; (void)workspace_bytes;
-    VFML_REQUIRE(fmap1 && fmap2 && levels, "corr_volume_pyramid: null pointer");
     VFML_REQUIRE(n_pairs >= 0 && C > 0 && h > 0 && w > 0, "corr_volume_pyramid: bad shape");
+    if (n_pairs == 0) return VFML_OK;
+    VFML_REQUIRE(fmap1 && fmap2 && levels, "corr_volume_pyramid: null pointer");
     VFML_REQUIRE(num_levels >= 1 && num_levels <= 4, "corr_volume_pyramid: num_levels %d not in 1..4", num_levels);
     VFML_REQUIRE(valid_dtype(vol_dtype), "corr_volume_pyramid: bad dtype");
     for (int l = 0; l < num_levels; ++l) VFML_REQUIRE(levels[l], "corr_volume_pyramid: level %d is null", l);

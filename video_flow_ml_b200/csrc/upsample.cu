@@ -158,7 +158,6 @@ extern "C" int vfml_convex_upsample8(const float* flow, const void* mask, int ma
                                      int mask_col, int mask_dtype, int n, int h, int w, float* out,
                                      int64_t out_stride_n, int64_t out_stride_c, int64_t out_stride_y,
                                      int crop_top, int crop_left, int out_h, int out_w, int flow_is_coords, vfml_stream_t s) {
-    VFML_REQUIRE(flow && mask && out, "convex_upsample8: null pointer");
     VFML_REQUIRE(n >= 0 && h > 0 && w > 0, "convex_upsample8: bad shape");
     VFML_REQUIRE(mask_layout == VFML_NCHW || mask_layout == VFML_ROWS, "convex_upsample8: bad layout");
     VFML_REQUIRE(valid_dtype(mask_dtype), "convex_upsample8: bad dtype");
@@ -168,6 +167,7 @@ extern "C" int vfml_convex_upsample8(const float* flow, const void* mask, int ma
         VFML_REQUIRE(mask_pitch >= mask_col + 576 && mask_col >= 0, "convex_upsample8: mask pitch %d too small", mask_pitch);
     if (mask_layout == VFML_NCHW) VFML_REQUIRE(mask_dtype == VFML_F32, "convex_upsample8: NCHW mask must be fp32");
     if (n == 0 || out_h == 0 || out_w == 0) return VFML_OK;
+    VFML_REQUIRE(flow && mask && out, "convex_upsample8: null pointer");
     UpParams p{flow, mask, mask_layout, mask_pitch, mask_col, n, h, w, out, out_stride_n, out_stride_c,
                out_stride_y, crop_top, crop_left, out_h, out_w, flow_is_coords};
     const int64_t total = (int64_t)n * h * w;

@@ -62,6 +62,18 @@ class TwinsStage01:
     @torch.no_grad()
     def __call__(self, x):
         """x [B, 3, H, W] in [-1, 1] -> [B, 256, H/8, W/8] fp32."""
+        if self.dtype != torch.float32 or not x.is_cuda:
+            return self._forward(x)
+        # fp32 tier: true fp32 library math (cuDNN / cuBLAS default to TF32 for convolutions)
+        c, m = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
+        try:
+            return self._forward(x)
+        finally:
+            torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = c, m
+
+    def _forward(self, x):
         x = x.to(self.dtype)
         B = x.shape[0]
         for s in range(2):
