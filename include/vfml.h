@@ -172,6 +172,9 @@ typedef struct vfml_gemm_desc {
  * GELU + residual chains of PCBlock4_Deep_nopool_res (stack.py:8-32), Attention.to_qk / q.k^T
  * (gma.py:54-74) and Aggregate's attn.v (gma.py:102-115). */
 int vfml_gemm(const vfml_gemm_desc* d, vfml_stream_t s);
+/* 1 if vfml_gemm would run this descriptor on the tcgen05 tensor-core kernel (fp16 operands, 16-byte
+ * aligned bases and pitches), 0 if on the exact fp32 FFMA kernel. */
+int vfml_gemm_uses_tensor_cores(const vfml_gemm_desc* d);
 
 /* Depthwise k x k convolution over rows layout with the PCBlock residual + GELU fused:
  *   y = gelu(x + dwconv_k(x) + b)     stack.py:25-26

@@ -135,3 +135,16 @@ def test_post_pass_wrappers(golden):
             assert o.dtype == want.dtype, (name, i, o.dtype, want.dtype)
             assert np.abs(o.astype(np.float64) - want).max() <= 1e-3, (name, i)
             prev = flows[i].copy()
+
+
+def test_mof_fp16_tier_matches_reference_golden(golden):
+    """Tensor-core tier (fp16 operands, fp32 accumulation, like the reference's own fp16 autocast on CUDA):
+    max EPE delta <= 5e-2 px vs the fp32 output of the unmodified reference (north-star reduced-precision bound)."""
+    from video_flow_ml_b200.processing import VideoFlowProcessor
+    g = golden("mof_e2e_g10.npz")
+    p = VideoFlowProcessor("cuda", sequence_length=5, precision="fp16")
+    p.core.load_state_dict(omof.mof_synthetic_weights(0, gain=1.0))
+    frames = cases.mof_case()
+    for idx in (2, 5):
+        flow = p.compute_optical_flow(list(frames), idx)
+        assert epe(flow, g[f"flow_{idx}"]) <= 5e-2, (idx, epe(flow, g[f"flow_{idx}"]))

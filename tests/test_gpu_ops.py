@@ -227,3 +227,52 @@ def test_misc_update_ops(ops):
     XI = rows_buf(Np, 16); XI.copy_(xin)
     ops.im2col3x3(XI, got, Fc, h, w)
     close(got, want, 0)
+
+
+# ---------------------------------------------------------------- tcgen05 GEMM (fp16 tier)
+def _aligned(t, dtype=torch.float16):
+    n, c = t.shape
+    buf = torch.zeros((n, (c + 7) // 8 * 8 + 8), dtype=dtype, device="cuda")
+    buf[:, :c] = t.to(dtype)
+    return buf[:, :c]
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (300, 128, 324), (1000, 486, 324), (257, 4, 192), (4224, 172, 600),
+                                   (129, 600, 400), (64, 48, 8), (2000, 1152, 256), (700, 700, 128), (128, 2050, 128)])
+def test_gemm_tensor_core(ops, M, N, K):
+    r = torch.Generator().manual_seed(M * 7 + N * 3 + K)
+    a = torch.randn((M, K), generator=r).half()
+    w = (torch.randn((N, K), generator=r) / K ** 0.5).half()
+    bias, dww, dwb = torch.randn(N, generator=r), torch.randn(N, generator=r) * 0.3, torch.randn(N, generator=r) * 0.3
+    res = torch.randn((M, N), generator=r).half()
+    A, Wt, R = _aligned(a), _aligned(w), _aligned(res)
+    for kw in (dict(), dict(bias=bias, act="gelu"), dict(bias=bias, res=res, act="gelu", dw=(dww, dwb)),
+               dict(bias=bias, act="relu", alpha=100.0), dict(res=res, alpha=0.5)):
+        want = torch.zeros((M, N), dtype=torch.float32)
+        fake_ops.gemm(a, w, want, **kw)
+        kwc = {k: (tuple(cu(x) for x in v) if isinstance(v, tuple) else v) for k, v in kw.items()}
+        if "bias" in kwc:
+            kwc["bias"] = cu(bias)
+        if "res" in kwc:
+            kwc["res"] = R
+        for odt in (torch.float16, torch.float32):
+            got = _aligned(torch.zeros((M, N)), odt)
+            ops.gemm(A, Wt, got, require_tc=True, **kwc)
+            close(got, want, 2e-3, 2e-3)
+
+
+def test_gemm_tensor_core_large_k_and_strided_views(ops):
+    """attention-shaped products: K = 7040 (110 k-blocks through the stage ring), operands that are column
+    slices of wider buffers."""
+    r = torch.Generator().manual_seed(9)
+    P = 1096
+    attn = torch.softmax(torch.randn((P, P), generator=r) * 2, -1).half()
+    vT = torch.randn((128, P), generator=r).half()
+    mf = torch.randn((P, 128), generator=r).half()
+    wide = torch.zeros((P, 512), dtype=torch.float16, device="cuda")
+    wide[:, 256:384] = mf.cuda()
+    want = torch.zeros((P, 128))
+    fake_ops.gemm(attn, vT, want, res=mf, alpha=0.5)
+    ops.gemm(_aligned(attn), _aligned(vT), wide[:, 384:512], res=wide[:, 256:384], alpha=0.5, require_tc=True)
+    close(wide[:, 384:512], want, 3e-3, 2e-3)
+    close(wide[:, 256:384], mf, 0)

@@ -20,3 +20,13 @@ void set_error(const char* fmt, ...) {
 extern "C" int vfml_version(void) { return VFML_VERSION; }
 extern "C" const char* vfml_last_error(void) { return vfml::g_err; }
 extern "C" uint64_t vfml_launch_count(void) { return vfml::g_launches.load(); }
+
+namespace vfml {
+bool gemm_tc_supported(const vfml_gemm_desc& d);
+int validate_gemm(const vfml_gemm_desc* d);
+}  // namespace vfml
+
+extern "C" int vfml_gemm_uses_tensor_cores(const vfml_gemm_desc* d) {
+    if (vfml::validate_gemm(d)) return 0;
+    return vfml::gemm_tc_supported(*d) ? 1 : 0;
+}

@@ -234,6 +234,8 @@ __global__ void im2col3x3_kernel(const T* __restrict__ x, T* __restrict__ out, i
 static inline int ew_blocks(int64_t n) { return (int)std::min<int64_t>((n + 255) / 256, 148 * 32); }
 
 int gemm_ffma(const vfml_gemm_desc& d, cudaStream_t st);
+int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st);
+bool gemm_tc_supported(const vfml_gemm_desc& d);
 int validate_gemm(const vfml_gemm_desc* d);
 
 }  // namespace vfml
@@ -276,6 +278,9 @@ extern "C" int vfml_gemm(const vfml_gemm_desc* d, vfml_stream_t s) {
     int rc = validate_gemm(d);
     if (rc) return rc;
     if (d->M == 0 || d->N == 0) return VFML_OK;
+    // fp16 operands with TMA-compatible alignment -> tcgen05 tensor-core kernel; fp32 (exact tier) and
+    // oddly aligned fp16 views -> FFMA kernel.  Both are libvfml kernels with identical semantics.
+    if (gemm_tc_supported(*d)) return gemm_tc(*d, to_stream(s));
     return gemm_ffma(*d, to_stream(s));
 }
 

@@ -29,12 +29,20 @@ def _pad8(c):
     return (c + 7) // 8 * 8
 
 
+def _pad_k(w):
+    """[N, K] weight as a rows view whose pitch is a multiple of 8 elements (16-byte rows: TMA requirement)."""
+    n, k = w.shape
+    buf = torch.zeros((n, _pad8(k)), dtype=w.dtype, device=w.device)
+    buf[:, :k] = w
+    return buf[:, :k]
+
+
 class _PCWeights:
     """PCBlock4_Deep_nopool_res parameters (stack.py:8-32) prepacked for the kernels."""
 
     def __init__(self, sd, p, k, dev, dt):
         g = lambda n: sd[f"{p}.{n}"].to(dev)
-        mat = lambda n: g(n + ".weight").flatten(1).to(dt).contiguous()
+        mat = lambda n: _pad_k(g(n + ".weight").flatten(1).to(dt))
         vec = lambda n: g(n + ".bias").float().contiguous()
         self.k = k
         self.w1a, self.b1a = mat("ffn1.0"), vec("ffn1.0")
@@ -70,14 +78,14 @@ class MOFEngine:
         self.convf1_w = sd[e + ".convf1_.weight"].to(dev).float().reshape(128, 4).contiguous()
         self.convf1_b = sd[e + ".convf1_.bias"].to(dev).float().contiguous()
         self.init_mhs = sd[e + ".init_hidden_state"].to(dev).float().reshape(48).contiguous()
-        self.w_v = sd["update_block.aggregator.to_v.weight"].to(dev).flatten(1).to(dt).contiguous()
+        self.w_v = _pad_k(sd["update_block.aggregator.to_v.weight"].to(dev).flatten(1).to(dt))
         self.gamma = float(sd["update_block.aggregator.gamma"].reshape(-1)[0])
-        self.w_qk = sd["att.to_qk.weight"].to(dev).flatten(1).to(dt).contiguous()
+        self.w_qk = _pad_k(sd["att.to_qk.weight"].to(dev).flatten(1).to(dt))
         # mask head (stack.py:120-124): conv3x3 128->256 as im2col GEMM with tap-major K, 1x1 256->1152, x100
         m0 = sd["update_block.mask.0.weight"].to(dev)                       # [256, 128, 3, 3]
-        self.w_m0 = m0.permute(0, 2, 3, 1).reshape(256, 9 * 128).to(dt).contiguous()
+        self.w_m0 = _pad_k(m0.permute(0, 2, 3, 1).reshape(256, 9 * 128).to(dt))
         self.b_m0 = sd["update_block.mask.0.bias"].to(dev).float().contiguous()
-        self.w_m2 = sd["update_block.mask.2.weight"].to(dev).flatten(1).to(dt).contiguous()
+        self.w_m2 = _pad_k(sd["update_block.mask.2.weight"].to(dev).flatten(1).to(dt))
         self.b_m2_x100 = (100.0 * sd["update_block.mask.2.bias"].to(dev).float()).contiguous()
         enc_dt = encoder_dtype or torch.float32
         self.fnet = TwinsStage01(sd, "fnet.svt", dev, enc_dt) if "fnet.svt.patch_embeds.0.proj.weight" in sd else None
@@ -100,13 +108,13 @@ class MOFEngine:
                 "x400": self._rows_buf(Np, 400),
                 "f128": self._rows_buf(Np, 128),
                 "x512": self._rows_buf(Np, 512),
-                "vT": self._rows_buf(128, Np),
+                "vT": torch.zeros((Fc, 128, _pad8(h * w)), dtype=self.dt, device=self.dev),
                 "delta": self._rows_buf(Np, 4, torch.float32),
                 "sa": self._rows_buf(2 * Np, 512),
                 "sb": self._rows_buf(2 * Np, 512),
                 "hid": self._rows_buf(2 * Np, 768),
                 "qk": self._rows_buf(Np, 256),
-                "attn": torch.empty((Fc, h * w, h * w), dtype=self.dt, device=self.dev),
+                "attn": torch.zeros((Fc, h * w, _pad8(h * w)), dtype=self.dt, device=self.dev),
                 "logits": torch.empty((h * w, h * w), dtype=torch.float32, device=self.dev),
                 "mask": self._rows_buf(Np, 576, torch.float32),
             }
@@ -171,7 +179,7 @@ class MOFEngine:
             q = ws["qk"][f * P:(f + 1) * P, 0:128]
             k = ws["qk"][f * P:(f + 1) * P, 128:256]
             o.gemm(q, k, ws["logits"], alpha=128 ** -0.5)
-            o.softmax_rows(ws["logits"], ws["attn"][f])
+            o.softmax_rows(ws["logits"], ws["attn"][f][:, :P])
 
     def update_step(self, ws, fpyr, bpyr, fc, bc, Fc, h, w):
         """One iteration of network.py:180-197 (lookups + SKUpdateBlock6..AllDecoder2, stack.py:127-140)."""
@@ -195,10 +203,11 @@ class MOFEngine:
                       [(slice(0, 124), full, x512[:, 256:380], None),
                        (slice(124, 172), full, x400[:, 352:400], None)])
         # Aggregate (gma.py:102-115): mfg = mf + gamma * attn @ to_v(mf)
-        o.gemm(self.w_v, mf, ws["vT"])
         for f in range(Fc):
-            o.gemm(ws["attn"][f], ws["vT"][:, f * P:(f + 1) * P], x512[f * P:(f + 1) * P, 384:512],
-                   res=mf[f * P:(f + 1) * P], alpha=self.gamma)
+            rows = slice(f * P, (f + 1) * P)
+            vT = ws["vT"][f][:, :P]
+            o.gemm(self.w_v, mf[rows], vT)                                   # to_v, transposed: [128, P]
+            o.gemm(ws["attn"][f][:, :P], vT, x512[rows, 384:512], res=mf[rows], alpha=self.gamma)
         self._pcblock(x512, self.gru, ws, Fc, h, w, [(full, full, x512[:, 0:128], None)])
         self._pcblock(x512[:, 0:128], self.fhead, ws, Fc, h, w, [(full, full, ws["delta"], None)])
         o.coords_add(fc, bc, ws["delta"])

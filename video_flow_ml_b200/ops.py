@@ -205,7 +205,7 @@ def taa(cur, flow, history, alpha, sigma_color, mode, hist_f32):
 
 
 # ------------------------------------------------------------------ update-step building blocks
-def gemm(a, w, out, bias=None, res=None, act=None, dw=None, alpha=1.0, addto=False):
+def gemm(a, w, out, bias=None, res=None, act=None, dw=None, alpha=1.0, addto=False, require_tc=False):
     """out[m, n] = epi(alpha * sum_k a[m, k] w[n, k]).  a, w, out, res: rows views."""
     _cuda(a, w, out, bias, res)
     _rows(a, "a"); _rows(w, "w"); _rows(out, "out")
@@ -240,6 +240,8 @@ def gemm(a, w, out, bias=None, res=None, act=None, dw=None, alpha=1.0, addto=Fal
         epi |= _lib.EPI_ADDTO
     d.epi = epi
     d.in_dtype, d.out_dtype = _dt(a), _dt(out)
+    if require_tc and not _lib.load().vfml_gemm_uses_tensor_cores(C.byref(d)):
+        raise RuntimeError("gemm: descriptor is not eligible for the tensor-core kernel (alignment / dtype)")
     _lib.check(_lib.load().vfml_gemm(C.byref(d), _stream()), "gemm")
     return out
 
