@@ -91,6 +91,13 @@ int vfml_corr_lookup(const void* const* levels, int num_levels, int vol_dtype, i
                      int w, int radius, const float* coords, void* out, int out_layout,
                      int out_pitch, int out_col, int out_dtype, vfml_stream_t s);
 
+/* Forward and backward lookups of one update iteration (network.py:185-186) as ONE launch, radius 4,
+ * rows layout: out_fwd / out_bwd are [n_frames*h*w, out_pitch] buffers. */
+int vfml_corr_lookup_pair(const void* const* levels_fwd, const void* const* levels_bwd, int num_levels,
+                          int vol_dtype, int n_frames, int h, int w, const float* coords_fwd,
+                          const float* coords_bwd, void* out_fwd, void* out_bwd, int out_pitch,
+                          int out_col, int out_dtype, vfml_stream_t s);
+
 /* ---------------------------------------------------------------------------------
  * Convex 8x upsampling (softmax over 9 taps fused).
  * Replaces MOFNet.upsample_flow, MOFNetStack/network.py:97-108.

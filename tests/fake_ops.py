@@ -53,6 +53,11 @@ def corr_lookup(levels, coords, radius=4, out=None, out_dtype=torch.float32):
     return out
 
 
+def corr_lookup_pair(levels_f, levels_b, coords_f, coords_b, out_f, out_b):
+    corr_lookup(levels_f, coords_f, 4, out=out_f)
+    corr_lookup(levels_b, coords_b, 4, out=out_b)
+
+
 def convex_upsample8(flow, mask, out=None, crop=None, flow_is_coords=False):
     n, _, h, w = flow.shape
     if flow_is_coords:

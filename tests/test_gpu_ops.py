@@ -276,3 +276,18 @@ def test_gemm_tensor_core_large_k_and_strided_views(ops):
     ops.gemm(_aligned(attn), _aligned(vT), wide[:, 384:512], res=wide[:, 256:384], alpha=0.5, require_tc=True)
     close(wide[:, 384:512], want, 3e-3, 2e-3)
     close(wide[:, 256:384], mf, 0)
+
+
+def test_lookup_pair_matches_single(ops):
+    r = np.random.default_rng(11)
+    n, h, w = 3, 24, 40
+    f1, f2, f3 = (r.standard_normal((n, 32, h, w)).astype(np.float32) for _ in range(3))
+    fp, bp = ops.corr_volume_pyramid(cu(f1), cu(f2), 4), ops.corr_volume_pyramid(cu(f1), cu(f3), 4)
+    cf = (omof.pixel_grid(n, h, w) + T((6 * r.standard_normal((n, 2, h, w))).astype(np.float32))).cuda()
+    cb = (omof.pixel_grid(n, h, w) + T((6 * r.standard_normal((n, 2, h, w))).astype(np.float32))).cuda()
+    both = rows_buf(2 * n * h * w, 324)
+    ops.corr_lookup_pair(fp, bp, cf, cb, both[:n * h * w], both[n * h * w:])
+    want_f = omof.corr_lookup(omof.corr_pyramid(T(f1), T(f2)), cf.cpu())
+    want_b = omof.corr_lookup(omof.corr_pyramid(T(f1), T(f3)), cb.cpu())
+    close(both[:n * h * w].view(n, h, w, 324).permute(0, 3, 1, 2), want_f, 5e-5)
+    close(both[n * h * w:].view(n, h, w, 324).permute(0, 3, 1, 2), want_b, 5e-5)

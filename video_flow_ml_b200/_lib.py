@@ -32,6 +32,7 @@ PROTOTYPES = {
     "vfml_corr_volume_workspace": (sz, [i32, i32, i32, i32, i32]),
     "vfml_corr_volume_pyramid": (i32, [vp, vp, i32, i32, i32, i32, C.POINTER(vp), i32, i32, vp, sz, vp]),
     "vfml_corr_lookup": (i32, [C.POINTER(vp), i32, i32, i32, i32, i32, i32, vp, vp, i32, i32, i32, i32, vp]),
+    "vfml_corr_lookup_pair": (i32, [C.POINTER(vp), C.POINTER(vp), i32, i32, i32, i32, i32, vp, vp, vp, vp, i32, i32, i32, vp]),
     "vfml_convex_upsample8": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, i64, i64, i64, i32, i32, i32, i32, i32, vp]),
     "vfml_encode_gamedev": (i32, [vp, vp, i32, i32, f32, f32, f32, f32, vp]),
     "vfml_encode_mv_rg8": (i32, [vp, vp, i32, i32, f32, vp]),

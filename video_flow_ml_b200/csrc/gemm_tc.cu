@@ -5,13 +5,18 @@
 // B = conv weight [Cout, Cin].  Same contract as the FFMA tier (gemm_ffma.cu); the reference runs
 // these layers under fp16 autocast on CUDA (MOFNetStack/network.py:149-192).
 //
-// One CTA = one 128 x BN output tile (BN runtime, multiple of 16, <= 256).  Warp 0 lane 0 issues
-// TMA loads of 128x64 (A) and BNx64 (B) fp16 boxes into a ring of stages; warp 1 lane 0 issues
-// tcgen05.mma (M=128, N=BN, K=16, 4 per stage) and commits stage release / accumulator-ready
-// mbarriers; warps 2-5 read the accumulator (each warp its own 32-lane TMEM quarter), apply
-// bias / residual / GELU / ReLU / the k=1 depthwise stage and store.  Out-of-range rows, columns
-// and the K tail are zero-filled by TMA, so no shape needs padding.  Shared memory is sized so
-// that two CTAs are resident per SM: one CTA's epilogue overlaps the other's MMA main loop.
+// Persistent kernel, one CTA per SM, static round-robin over 128 x BN output tiles (BN runtime,
+// multiple of 16, <= 256).  Warp 0 lane 0 issues TMA loads of 128x64 (A) and BNx64 (B) fp16 boxes
+// into a ring of stages that keeps running across tiles; warp 1 lane 0 issues tcgen05.mma (M=128,
+// N=BN, K=16, 4 per stage) into one of TWO 256-column TMEM accumulators; warps 2-9 drain the other
+// accumulator (each warp its own 32-lane TMEM quarter and half of the columns), apply
+// bias / residual / GELU / ReLU / the k=1 depthwise stage and store, so the epilogue of tile i
+// overlaps the MMA main loop of tile i+1.  Out-of-range rows, columns and the K tail are
+// zero-filled by TMA, so no shape needs padding.
+//
+// The epilogue is the co-bottleneck of these small-K GEMMs (K = 128..768), so its math is packed:
+// fp32 pairs through fma.rn.f32x2, and GELU through a degree-12 polynomial in x^2 of
+// (Phi(x) - 1/2) / x on |x| <= 5 (max abs error 2e-6, no MUFU ops).
 #include <cuda.h>
 
 #include "common.cuh"
@@ -19,8 +24,10 @@
 namespace vfml {
 
 constexpr int TC_BM = 128, TC_BK = 64;
-constexpr int TC_THREADS = 192;
-constexpr int TC_MAX_STAGES = 6;
+constexpr int TC_EPI_WARPS = 8;
+constexpr int TC_THREADS = 64 + TC_EPI_WARPS * 32;
+constexpr int TC_MAX_STAGES = 8;
+constexpr int TC_VEC_MAX = 2048;      // columns of bias / dw vectors staged in shared memory
 
 struct TcParams {
     void* D;
@@ -29,11 +36,12 @@ struct TcParams {
     const float* dw_w;
     const float* dw_b;
     int64_t ldd, ldr, strideD, strideR;
-    int M, N, K;
-    int BN, stages;
+    int M, N, K, batch;
+    int BN, stages, m_tiles, n_tiles;
     float alpha;
     uint32_t epi;
     int out_f32;
+    int vec_in_smem;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -43,6 +51,9 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
 }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     asm volatile(
@@ -94,7 +105,51 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
     return d;
 }
 
-__global__ void __launch_bounds__(TC_THREADS)
+// ---- packed fp32 pair arithmetic (Blackwell FFMA2 / FMUL2 / FADD2)
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
+    float2 d;
+    asm("{\n.reg .b64 ra, rb, rc, rd;\nmov.b64 ra, {%2, %3};\nmov.b64 rb, {%4, %5};\nmov.b64 rc, {%6, %7};\n"
+        "fma.rn.f32x2 rd, ra, rb, rc;\nmov.b64 {%0, %1}, rd;\n}"
+        : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+    return d;
+}
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+    float2 d;
+    asm("{\n.reg .b64 ra, rb, rd;\nmov.b64 ra, {%2, %3};\nmov.b64 rb, {%4, %5};\nmul.rn.f32x2 rd, ra, rb;\nmov.b64 {%0, %1}, rd;\n}"
+        : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+    return d;
+}
+__device__ __forceinline__ float2 add2(float2 a, float2 b) {
+    float2 d;
+    asm("{\n.reg .b64 ra, rb, rd;\nmov.b64 ra, {%2, %3};\nmov.b64 rb, {%4, %5};\nadd.rn.f32x2 rd, ra, rb;\nmov.b64 {%0, %1}, rd;\n}"
+        : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+    return d;
+}
+__device__ __forceinline__ float2 splat(float v) { return make_float2(v, v); }
+
+// gelu(x) = x * Phi(x);  Phi(x) - 1/2 = x * R(s),  s = x^2 * (2/25) - 1,  |x| clamped to 5.
+// R: degree-12 Chebyshev fit converted to monomials in s (well conditioned on [-1, 1]); max abs error of
+// gelu over all x: 2e-6 (tests/test_gelu_poly.py), far below the fp16 rounding of the stored result.
+__device__ __forceinline__ float2 gelu_poly2(float2 x) {
+    const float2 xc = make_float2(fminf(fmaxf(x.x, -5.0f), 5.0f), fminf(fmaxf(x.y, -5.0f), 5.0f));
+    const float2 s = fma2(mul2(xc, xc), splat(0.08f), splat(-1.0f));
+    float2 r = splat(7.353763795e-04f);
+    r = fma2(r, s, splat(-1.676730928e-03f));
+    r = fma2(r, s, splat(1.374596148e-03f));
+    r = fma2(r, s, splat(-2.526916796e-03f));
+    r = fma2(r, s, splat(6.766527425e-03f));
+    r = fma2(r, s, splat(-1.130712498e-02f));
+    r = fma2(r, s, splat(1.623608917e-02f));
+    r = fma2(r, s, splat(-2.321312763e-02f));
+    r = fma2(r, s, splat(3.147675842e-02f));
+    r = fma2(r, s, splat(-4.045128077e-02f));
+    r = fma2(r, s, splat(5.151792988e-02f));
+    r = fma2(r, s, splat(-7.029590756e-02f));
+    r = fma2(r, s, splat(1.413638145e-01f));
+    return mul2(x, fma2(xc, r, splat(0.5f)));
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const TcParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -103,26 +158,40 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     const uint32_t b_stride = (b_bytes + 1023) & ~1023u;
     uint8_t* sA = smem;
     uint8_t* sB = smem + (size_t)stages * a_bytes;
-    __shared__ uint64_t full_bar[TC_MAX_STAGES], empty_bar[TC_MAX_STAGES], acc_bar;
+    float* s_vec = reinterpret_cast<float*>(sB + (size_t)stages * b_stride);     // [3][vec_cols]: bias, dw_w, dw_b
+    __shared__ uint64_t full_bar[TC_MAX_STAGES], empty_bar[TC_MAX_STAGES], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_base_s;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.y * TC_BM, n0 = blockIdx.x * BN, bz = blockIdx.z;
     const int nkb = (p.K + TC_BK - 1) / TC_BK;
+    const int tiles_per_batch = p.m_tiles * p.n_tiles;
+    const int num_tiles = tiles_per_batch * p.batch;
+    const int vec_cols = p.n_tiles * BN;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < stages; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
-        mbar_init(&acc_bar, 1);
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&acc_full[b], 1);
+            mbar_init(&acc_empty[b], TC_EPI_WARPS);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(256u) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(512u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (p.vec_in_smem && warp >= 2) {
+        for (int i = threadIdx.x - 64; i < vec_cols; i += TC_EPI_WARPS * 32) {
+            const bool ok = i < p.N;
+            s_vec[i] = (ok && (p.epi & VFML_EPI_BIAS)) ? p.bias[i] : 0.0f;
+            s_vec[vec_cols + i] = (ok && (p.epi & VFML_EPI_DW1)) ? p.dw_w[i] : 0.0f;
+            s_vec[2 * vec_cols + i] = (ok && (p.epi & VFML_EPI_DW1)) ? p.dw_b[i] : 0.0f;
+        }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -131,114 +200,173 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 
     if (warp == 0) {
         if (lane == 0) {
-            for (int kb = 0; kb < nkb; ++kb) {
-                const int s = kb % stages;
-                const uint32_t ph = (uint32_t)(kb / stages) & 1u;
-                mbar_wait(&empty_bar[s], ph ^ 1u);
-                mbar_expect_tx(&full_bar[s], a_bytes + b_bytes);
-                tma_load_3d(&mapA, &full_bar[s], sA + (size_t)s * a_bytes, kb * TC_BK, m0, bz);
-                tma_load_3d(&mapB, &full_bar[s], sB + (size_t)s * b_stride, kb * TC_BK, n0, bz);
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int bz = tile / tiles_per_batch, t = tile - bz * tiles_per_batch;
+                const int m0 = (t / p.n_tiles) * TC_BM, n0 = (t % p.n_tiles) * BN;
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int s = it % stages;
+                    const uint32_t ph = (it / stages) & 1u;
+                    mbar_wait(&empty_bar[s], ph ^ 1u);
+                    mbar_expect_tx(&full_bar[s], a_bytes + b_bytes);
+                    tma_load_3d(&mapA, &full_bar[s], sA + (size_t)s * a_bytes, kb * TC_BK, m0, bz);
+                    tma_load_3d(&mapB, &full_bar[s], sB + (size_t)s * b_stride, kb * TC_BK, n0, bz);
+                }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
             // instruction descriptor: D fp32, A/B fp16, both K-major, N = BN, M = 128
             const uint32_t idesc = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
-            for (int kb = 0; kb < nkb; ++kb) {
-                const int s = kb % stages;
-                const uint32_t ph = (uint32_t)(kb / stages) & 1u;
-                mbar_wait(&full_bar[s], ph);
+            uint32_t it = 0, tl = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
+                const uint32_t buf = tl & 1u, aph = (tl >> 1) & 1u;
+                mbar_wait(&acc_empty[buf], aph ^ 1u);          // epilogue has drained this accumulator
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint64_t adesc = make_sw128_desc(smem_u32(sA + (size_t)s * a_bytes));
-                const uint64_t bdesc = make_sw128_desc(smem_u32(sB + (size_t)s * b_stride));
+                const uint32_t tmem_d = tmem_base + buf * 256u;
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int s = it % stages;
+                    const uint32_t ph = (it / stages) & 1u;
+                    mbar_wait(&full_bar[s], ph);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint64_t adesc = make_sw128_desc(smem_u32(sA + (size_t)s * a_bytes));
+                    const uint64_t bdesc = make_sw128_desc(smem_u32(sB + (size_t)s * b_stride));
 #pragma unroll
-                for (int k = 0; k < TC_BK / 16; ++k) {
-                    // +32 bytes per K=16 step inside the 128-byte swizzle atom
-                    umma_f16(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) ? 1u : 0u);
+                    for (int k = 0; k < TC_BK / 16; ++k)   // +32 bytes per K=16 step inside the 128-byte swizzle atom
+                        umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) ? 1u : 0u);
+                    umma_commit(&empty_bar[s]);
                 }
-                umma_commit(&empty_bar[s]);
+                umma_commit(&acc_full[buf]);
             }
-            umma_commit(&acc_bar);
         }
     } else {
         const int q = warp & 3;                   // TMEM lane quarter this warp may access
-        const int m = m0 + q * 32 + lane;
-        mbar_wait(&acc_bar, 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const bool row_ok = m < p.M;
-        const __half* rrow = p.res ? p.res + bz * p.strideR + (int64_t)m * p.ldr : nullptr;
-        __half* d16 = reinterpret_cast<__half*>(p.D) + bz * p.strideD + (int64_t)m * p.ldd;
-        float* d32 = reinterpret_cast<float*>(p.D) + bz * p.strideD + (int64_t)m * p.ldd;
-        for (int c = 0; c < BN; c += 16) {
-            const int n = n0 + c;
-            if (n >= p.N) break;                  // warp-uniform
-            float v[16];
-            tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
-            if (!row_ok) continue;
-            const bool full = n + 16 <= p.N;
-            float r[16];
-            if (p.epi & VFML_EPI_RES) {
-                if (full && ((reinterpret_cast<uintptr_t>(rrow + n) & 15) == 0)) {
-                    const uint4 t0 = *reinterpret_cast<const uint4*>(rrow + n);
-                    const uint4 t1 = *reinterpret_cast<const uint4*>(rrow + n + 8);
-                    const __half2* h0 = reinterpret_cast<const __half2*>(&t0);
-                    const __half2* h1 = reinterpret_cast<const __half2*>(&t1);
+        const int hsel = (warp - 2) >> 2;         // which half of the 16-column chunks
+        const bool has_bias = p.epi & VFML_EPI_BIAS, has_res = p.epi & VFML_EPI_RES, has_dw = p.epi & VFML_EPI_DW1;
+        const bool do_gelu = p.epi & VFML_EPI_GELU, do_relu = p.epi & VFML_EPI_RELU;
+        const float2 alpha2 = splat(p.alpha);
+        uint32_t tl = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
+            const int bz = tile / tiles_per_batch, t = tile - bz * tiles_per_batch;
+            const int m0 = (t / p.n_tiles) * TC_BM, n0 = (t % p.n_tiles) * BN;
+            const uint32_t buf = tl & 1u, aph = (tl >> 1) & 1u;
+            const int m = m0 + q * 32 + lane;
+            const bool row_ok = m < p.M;
+            const __half* rrow = p.res ? p.res + bz * p.strideR + (int64_t)m * p.ldr : nullptr;
+            __half* d16 = reinterpret_cast<__half*>(p.D) + bz * p.strideD + (int64_t)m * p.ldd;
+            float* d32 = reinterpret_cast<float*>(p.D) + bz * p.strideD + (int64_t)m * p.ldd;
+            mbar_wait(&acc_full[buf], aph);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            for (int c = hsel * 16; c < BN; c += 32) {
+                const int n = n0 + c;
+                if (n >= p.N) break;                  // warp-uniform
+                float v[16];
+                tmem_ld16(tmem_base + buf * 256u + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
+                if (!row_ok) continue;
+                const bool full = n + 16 <= p.N;
+                float2 x[8];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const float2 f0 = __half22float2(h0[i]), f1 = __half22float2(h1[i]);
-                        r[2 * i] = f0.x; r[2 * i + 1] = f0.y; r[8 + 2 * i] = f1.x; r[8 + 2 * i + 1] = f1.y;
+                for (int i = 0; i < 8; ++i) x[i] = mul2(make_float2(v[2 * i], v[2 * i + 1]), alpha2);
+                if (has_bias) {
+                    if (p.vec_in_smem) {
+                        const float4* b4 = reinterpret_cast<const float4*>(s_vec + (n - 0));
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float4 b = b4[i];
+                            x[2 * i] = add2(x[2 * i], make_float2(b.x, b.y));
+                            x[2 * i + 1] = add2(x[2 * i + 1], make_float2(b.z, b.w));
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            x[i] = add2(x[i], make_float2(__ldg(p.bias + min(n + 2 * i, p.N - 1)), __ldg(p.bias + min(n + 2 * i + 1, p.N - 1))));
+                    }
+                }
+                if (has_res) {
+                    if (full && ((reinterpret_cast<uintptr_t>(rrow + n) & 15) == 0)) {
+                        const uint4 t0 = *reinterpret_cast<const uint4*>(rrow + n);
+                        const uint4 t1 = *reinterpret_cast<const uint4*>(rrow + n + 8);
+                        const __half2* h0 = reinterpret_cast<const __half2*>(&t0);
+                        const __half2* h1 = reinterpret_cast<const __half2*>(&t1);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            x[i] = add2(x[i], __half22float2(h0[i]));
+                            x[4 + i] = add2(x[4 + i], __half22float2(h1[i]));
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            x[i] = add2(x[i], make_float2(n + 2 * i < p.N ? __half2float(rrow[n + 2 * i]) : 0.0f,
+                                                          n + 2 * i + 1 < p.N ? __half2float(rrow[n + 2 * i + 1]) : 0.0f));
+                    }
+                }
+                if (do_gelu) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) x[i] = gelu_poly2(x[i]);
+                }
+                if (do_relu) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) x[i] = make_float2(fmaxf(x[i].x, 0.0f), fmaxf(x[i].y, 0.0f));
+                }
+                if (has_dw) {   // k = 1 depthwise stage: gelu(v + (w * v + b))
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        float2 w2, b2;
+                        if (p.vec_in_smem) {
+                            w2 = *reinterpret_cast<const float2*>(s_vec + vec_cols + n + 2 * i);
+                            b2 = *reinterpret_cast<const float2*>(s_vec + 2 * vec_cols + n + 2 * i);
+                        } else {
+                            const int n1 = min(n + 2 * i, p.N - 1), n2 = min(n + 2 * i + 1, p.N - 1);
+                            w2 = make_float2(__ldg(p.dw_w + n1), __ldg(p.dw_w + n2));
+                            b2 = make_float2(__ldg(p.dw_b + n1), __ldg(p.dw_b + n2));
+                        }
+                        x[i] = gelu_poly2(add2(x[i], fma2(w2, x[i], b2)));
+                    }
+                }
+                if (p.out_f32) {
+                    if (full && ((reinterpret_cast<uintptr_t>(d32 + n) & 15) == 0)) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            *reinterpret_cast<float4*>(d32 + n + 4 * i) = make_float4(x[2 * i].x, x[2 * i].y, x[2 * i + 1].x, x[2 * i + 1].y);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            if (n + 2 * i < p.N) d32[n + 2 * i] = x[i].x;
+                            if (n + 2 * i + 1 < p.N) d32[n + 2 * i + 1] = x[i].y;
+                        }
                     }
                 } else {
+                    if (full && ((reinterpret_cast<uintptr_t>(d16 + n) & 15) == 0)) {
+                        uint4 o0, o1;
+                        __half2* h0 = reinterpret_cast<__half2*>(&o0);
+                        __half2* h1 = reinterpret_cast<__half2*>(&o1);
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) r[i] = (n + i < p.N) ? __half2float(rrow[n + i]) : 0.0f;
-                }
-            }
+                        for (int i = 0; i < 4; ++i) {
+                            h0[i] = __float22half2_rn(x[i]);
+                            h1[i] = __float22half2_rn(x[4 + i]);
+                        }
+                        *reinterpret_cast<uint4*>(d16 + n) = o0;
+                        *reinterpret_cast<uint4*>(d16 + n + 8) = o1;
+                    } else {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                const int nn = min(n + i, p.N - 1);
-                float x = v[i] * p.alpha;
-                if (p.epi & VFML_EPI_BIAS) x += __ldg(p.bias + nn);
-                if (p.epi & VFML_EPI_RES) x += r[i];
-                if (p.epi & VFML_EPI_GELU) x = gelu_erf(x);
-                if (p.epi & VFML_EPI_RELU) x = fmaxf(x, 0.0f);
-                if (p.epi & VFML_EPI_DW1) x = gelu_erf(x + (__ldg(p.dw_w + nn) * x + __ldg(p.dw_b + nn)));
-                v[i] = x;
-            }
-            if (p.out_f32) {
-                if (full && ((reinterpret_cast<uintptr_t>(d32 + n) & 15) == 0)) {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        *reinterpret_cast<float4*>(d32 + n + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 16; ++i)
-                        if (n + i < p.N) d32[n + i] = v[i];
-                }
-            } else {
-                if (full && ((reinterpret_cast<uintptr_t>(d16 + n) & 15) == 0)) {
-                    uint4 o0, o1;
-                    __half2* h0 = reinterpret_cast<__half2*>(&o0);
-                    __half2* h1 = reinterpret_cast<__half2*>(&o1);
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        h0[i] = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
-                        h1[i] = __floats2half2_rn(v[8 + 2 * i], v[8 + 2 * i + 1]);
+                        for (int i = 0; i < 8; ++i) {
+                            if (n + 2 * i < p.N) d16[n + 2 * i] = __float2half_rn(x[i].x);
+                            if (n + 2 * i + 1 < p.N) d16[n + 2 * i + 1] = __float2half_rn(x[i].y);
+                        }
                     }
-                    *reinterpret_cast<uint4*>(d16 + n) = o0;
-                    *reinterpret_cast<uint4*>(d16 + n + 8) = o1;
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 16; ++i)
-                        if (n + i < p.N) d16[n + i] = __float2half_rn(v[i]);
                 }
             }
+            // this warp is done reading the accumulator: hand it back to the MMA warp
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[buf]);
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256u) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
     }
 }
 
@@ -265,9 +393,9 @@ static int make_map(CUtensorMap* map, const void* base, int64_t inner, int64_t r
         }
         encode = reinterpret_cast<encode_fn_t>(fn);
     }
-    CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), dims, strides, box,
-                                        estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         set_error("gemm_tc: cuTensorMapEncodeTiled failed: CUresult %d (inner=%lld rows=%lld batch=%lld ld=%lld)", (int)r,
                   (long long)inner, (long long)rows, (long long)batch, (long long)ld);
@@ -300,22 +428,29 @@ int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st) {
     if (rc) return rc;
     rc = make_map(&mapB, d.B, d.K, d.N, d.batch, d.ldb, d.strideB, BN);
     if (rc) return rc;
-    const int nkb = (d.K + TC_BK - 1) / TC_BK;
-    const size_t a_bytes = TC_BM * TC_BK * 2, b_stride = ((size_t)BN * TC_BK * 2 + 1023) & ~(size_t)1023;
-    int stages = (int)((110 * 1024 - 1024) / (a_bytes + b_stride));     // two CTAs per SM
-    stages = std::max(2, std::min(std::min(stages, TC_MAX_STAGES), std::max(nkb, 2)));
-    const size_t smem = 1024 + stages * (a_bytes + b_stride);
-    static bool attr_done = false;
-    if (!attr_done) {
-        VFML_CUDA(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_done = true;
-    }
     TcParams p{};
+    p.m_tiles = cdiv(d.M, TC_BM);
+    p.n_tiles = cdiv(d.N, BN);
+    const bool needs_vec = d.epi & (VFML_EPI_BIAS | VFML_EPI_DW1);
+    p.vec_in_smem = needs_vec && p.n_tiles * BN <= TC_VEC_MAX;
+    const size_t vec_bytes = p.vec_in_smem ? (size_t)3 * p.n_tiles * BN * sizeof(float) : 0;
+    const size_t a_bytes = TC_BM * TC_BK * 2, b_stride = ((size_t)BN * TC_BK * 2 + 1023) & ~(size_t)1023;
+    int stages = (int)((200 * 1024 - 1024 - vec_bytes) / (a_bytes + b_stride));
+    stages = std::max(2, std::min(stages, TC_MAX_STAGES));
+    const size_t smem = 1024 + stages * (a_bytes + b_stride) + vec_bytes;
+    static int num_sms = 0;
+    if (!num_sms) {
+        int dev = 0;
+        VFML_CUDA(cudaGetDevice(&dev));
+        VFML_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+        VFML_CUDA(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 512));
+    }
     p.D = d.D; p.bias = d.bias; p.res = reinterpret_cast<const __half*>(d.res); p.dw_w = d.dw_w; p.dw_b = d.dw_b;
     p.ldd = d.ldd; p.ldr = d.ldr; p.strideD = d.strideD; p.strideR = d.strideR;
-    p.M = d.M; p.N = d.N; p.K = d.K; p.BN = BN; p.stages = stages;
+    p.M = d.M; p.N = d.N; p.K = d.K; p.batch = d.batch; p.BN = BN; p.stages = stages;
     p.alpha = d.alpha; p.epi = d.epi; p.out_f32 = d.out_dtype == VFML_F32;
-    dim3 grid(cdiv(d.N, BN), cdiv(d.M, TC_BM), d.batch);
+    const int64_t num_tiles = (int64_t)p.m_tiles * p.n_tiles * d.batch;
+    const int grid = (int)std::min<int64_t>(num_tiles, num_sms);
     gemm_tc_kernel<<<grid, TC_THREADS, smem, st>>>(mapA, mapB, p);
     VFML_LAUNCH_CHECK("gemm_tc");
     return VFML_OK;

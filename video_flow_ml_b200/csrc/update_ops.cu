@@ -233,6 +233,8 @@ __global__ void im2col3x3_kernel(const T* __restrict__ x, T* __restrict__ out, i
 
 static inline int ew_blocks(int64_t n) { return (int)std::min<int64_t>((n + 255) / 256, 148 * 32); }
 
+int dwconv_tiled(const void* x, void* y, int n_img, int h, int w, int C, int64_t px, int64_t py, const float* wgt,
+                 const float* bias, int k, int dtype, cudaStream_t st);
 int gemm_ffma(const vfml_gemm_desc& d, cudaStream_t st);
 int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st);
 bool gemm_tc_supported(const vfml_gemm_desc& d);
@@ -292,6 +294,11 @@ extern "C" int vfml_dwconv_res_gelu(const void* x, void* y, int n_img, int h, in
     VFML_REQUIRE(valid_dtype(dtype), "dwconv: bad dtype");
     if (n_img == 0) return VFML_OK;
     VFML_REQUIRE(x && y && weight && bias && x != y, "dwconv: null or aliased pointer");
+    {   // k = 15 / 7 with vector-aligned channels: shared-memory tiled kernel (dwconv.cu)
+        const int rc = dwconv_tiled(x, y, n_img, h, w, C, pitch_x, pitch_y, weight, bias, k, dtype, to_stream(s));
+        if (rc < 0) return rc;
+        if (rc == 1) return VFML_OK;
+    }
     const int64_t total = (int64_t)n_img * h * w * C;
     DISPATCH_T(dtype, (dwconv_res_gelu_kernel<float><<<ew_blocks(total), 256, 0, to_stream(s)>>>((const float*)x, (float*)y, n_img, h, w, C, pitch_x, pitch_y, weight, bias, k)),
                (dwconv_res_gelu_kernel<__half><<<ew_blocks(total), 256, 0, to_stream(s)>>>((const __half*)x, (__half*)y, n_img, h, w, C, pitch_x, pitch_y, weight, bias, k)));

@@ -187,8 +187,7 @@ class MOFEngine:
         P = h * w
         Np = Fc * P
         corr2, x400, x512 = ws["corr2"], ws["x400"], ws["x512"]
-        o.corr_lookup(fpyr, fc, CORR_RADIUS, out=corr2[:Np])
-        o.corr_lookup(bpyr, bc, CORR_RADIUS, out=corr2[Np:])
+        o.corr_lookup_pair(fpyr, bpyr, fc, bc, corr2[:Np], corr2[Np:])
         mf = x512[:, 256:384]
         o.motion_glue(fc, bc, x400, ws["f128"], mf, self.convf1_w, self.convf1_b, Fc, h, w)
         full = slice(None)

@@ -123,6 +123,23 @@ def corr_lookup(levels, coords, radius=4, out=None, out_dtype=torch.float32):
     return out
 
 
+def corr_lookup_pair(levels_f, levels_b, coords_f, coords_b, out_f, out_b):
+    """Forward + backward radius-4 lookups in one launch; out_f / out_b: rows views [n*h*w, 324] of equal pitch."""
+    _cuda(coords_f, coords_b, out_f, out_b, *levels_f, *levels_b)
+    _f32c(coords_f, "coords_f"); _f32c(coords_b, "coords_b")
+    _rows(out_f, "out_f"); _rows(out_b, "out_b")
+    n, _, h, w = coords_f.shape
+    L = len(levels_f)
+    if (coords_b.shape != coords_f.shape or len(levels_b) != L or out_f.shape != (n * h * w, L * 81)
+            or out_b.shape != out_f.shape or out_f.stride(0) != out_b.stride(0) or out_f.dtype != out_b.dtype
+            or levels_f[0].shape != levels_b[0].shape or levels_f[0].shape[0] != n * h * w):
+        raise ValueError("corr_lookup_pair: shape mismatch")
+    af = (C.c_void_p * L)(*[l.data_ptr() for l in levels_f])
+    ab = (C.c_void_p * L)(*[l.data_ptr() for l in levels_b])
+    _lib.check(_lib.load().vfml_corr_lookup_pair(af, ab, L, _dt(levels_f[0]), n, h, w, _p(coords_f), _p(coords_b), _p(out_f),
+                                                 _p(out_b), out_f.stride(0), 0, _dt(out_f), _stream()), "corr_lookup_pair")
+
+
 def convex_upsample8(flow, mask, out=None, crop=None, flow_is_coords=False):
     """flow [n, 2, h, w] fp32; mask [n, 576, h, w] fp32 or rows view [n*h*w, 576].
     crop=(top, left, out_h, out_w) selects a window of the 8h x 8w result (unpad fused);
