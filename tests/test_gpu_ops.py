@@ -291,3 +291,13 @@ def test_lookup_pair_matches_single(ops):
     want_b = omof.corr_lookup(omof.corr_pyramid(T(f1), T(f3)), cb.cpu())
     close(both[:n * h * w].view(n, h, w, 324).permute(0, 3, 1, 2), want_f, 5e-5)
     close(both[n * h * w:].view(n, h, w, 324).permute(0, 3, 1, 2), want_b, 5e-5)
+
+
+def test_corrblock_dropin(ops, golden):
+    from video_flow_ml_b200.corr import CorrBlock
+    g = golden("corr_lookup.npz")
+    f1, f2, coords = cases.lookup_case()
+    blk = CorrBlock(cu(f1), cu(f2), num_levels=4, radius=4)
+    assert len(blk.corr_pyramid) == 4 and blk.corr_pyramid[0].shape == (768, 1, 16, 24)
+    close(blk(cu(coords)), T(g["lookup"]), 5e-5)
+    close(CorrBlock.corr(cu(f1), cu(f2))[0, :2], T(g["vol0"]), 2e-5)
