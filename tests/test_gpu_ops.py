@@ -293,6 +293,19 @@ def test_lookup_pair_matches_single(ops):
     close(both[n * h * w:].view(n, h, w, 324).permute(0, 3, 1, 2), want_b, 5e-5)
 
 
+@pytest.mark.parametrize("n,C,h,w", [(2, 256, 16, 24), (3, 64, 20, 31), (1, 256, 55, 128)])
+def test_volume_fp16_tensor_core(ops, n, C, h, w):
+    """fp16 tier: volume through the tcgen05 GEMM (fp16 operands, fp32 accumulate, fp16 storage) + pyramid."""
+    r = np.random.default_rng(21)
+    f1 = r.standard_normal((n, C, h, w)).astype(np.float32)
+    f2 = r.standard_normal((n, C, h, w)).astype(np.float32)
+    want = omof.corr_pyramid(T(f1).half().float(), T(f2).half().float())
+    got = ops.corr_volume_pyramid(cu(f1), cu(f2), 4, torch.float16)
+    for a, b in zip(got, want):
+        assert a.dtype == torch.float16 and a.shape == b.shape
+        close(a, b, 4e-3, 2e-3)
+
+
 def test_corrblock_dropin(ops, golden):
     from video_flow_ml_b200.corr import CorrBlock
     g = golden("corr_lookup.npz")

@@ -133,7 +133,55 @@ static int run_volume(const float* f1, const float* f2, int n_pairs, int C, int 
 
 using namespace vfml;
 
-extern "C" size_t vfml_corr_volume_workspace(int, int, int, int, int) { return 0; }
+// fp16 tier: the volume is a dense contraction -> tensor cores.  Both feature maps are transposed to
+// pixel-major fp16 rows ([P, C], K contiguous) in the caller's workspace and multiplied by the tcgen05
+// GEMM (batch = pairs, alpha = 1/sqrt(C), fp16 output straight into level 0); the pyramid follows.
+static bool volume_uses_tc(int C, int vol_dtype) { return vol_dtype == VFML_F16 && (C % 8) == 0; }
+
+extern "C" size_t vfml_corr_volume_workspace(int n_pairs, int C, int h, int w, int vol_dtype) {
+    if (!volume_uses_tc(C, vol_dtype)) return 0;
+    return (size_t)2 * n_pairs * h * w * C * sizeof(__half) + 256;
+}
+
+static int run_volume_tc(const float* f1, const float* f2, int n_pairs, int C, int h, int w, void* const* levels,
+                         int num_levels, void* workspace, size_t workspace_bytes, vfml_stream_t s) {
+    const int P = h * w;
+    const size_t need = vfml_corr_volume_workspace(n_pairs, C, h, w, VFML_F16);
+    if (!workspace || workspace_bytes < need) {
+        set_error("corr_volume_pyramid: workspace of %zu bytes needed, %zu given", need, workspace_bytes);
+        return VFML_ERR_WORKSPACE;
+    }
+    __half* r1 = reinterpret_cast<__half*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~(uintptr_t)255);
+    __half* r2 = r1 + (size_t)n_pairs * P * C;
+    int rc = vfml_nchw_to_rows(f1, r1, n_pairs, C, P, C, 0, VFML_F16, s);
+    if (rc) return rc;
+    rc = vfml_nchw_to_rows(f2, r2, n_pairs, C, P, C, 0, VFML_F16, s);
+    if (rc) return rc;
+    vfml_gemm_desc d{};
+    d.A = r1; d.B = r2; d.D = levels[0];
+    d.lda = C; d.ldb = C; d.ldd = P;
+    d.M = P; d.N = P; d.K = C; d.batch = n_pairs;
+    d.strideA = (int64_t)P * C; d.strideB = (int64_t)P * C; d.strideD = (int64_t)P * P;
+    d.alpha = 1.0f / sqrtf((float)C);
+    d.in_dtype = VFML_F16; d.out_dtype = VFML_F16;
+    rc = vfml_gemm(&d, s);
+    if (rc) return rc;
+    cudaStream_t st = to_stream(s);
+    int hi = h, wi = w;
+    for (int l = 1; l < num_levels; ++l) {
+        const int64_t rows = (int64_t)n_pairs * P;
+        const int64_t total = rows * (hi / 2) * (wi / 2);
+        if (total > 0) {
+            const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 32);
+            corr_pool_kernel<__half><<<blocks, 256, 0, st>>>(reinterpret_cast<const __half*>(levels[l - 1]),
+                                                            reinterpret_cast<__half*>(levels[l]), rows, hi, wi);
+            VFML_LAUNCH_CHECK("corr_pool");
+        }
+        hi /= 2;
+        wi /= 2;
+    }
+    return VFML_OK;
+}
 
 extern "C" int vfml_corr_volume_pyramid(const float* fmap1, const float* fmap2, int n_pairs, int C, int h, int w,
                                         void* const* levels, int num_levels, int vol_dtype, void* workspace,
@@ -145,7 +193,8 @@ extern "C" int vfml_corr_volume_pyramid(const float* fmap1, const float* fmap2, 
     VFML_REQUIRE(num_levels >= 1 && num_levels <= 4, "corr_volume_pyramid: num_levels %d not in 1..4", num_levels);
     VFML_REQUIRE(valid_dtype(vol_dtype), "corr_volume_pyramid: bad dtype");
     for (int l = 0; l < num_levels; ++l) VFML_REQUIRE(levels[l], "corr_volume_pyramid: level %d is null", l);
-    if (n_pairs == 0) return VFML_OK;
+    if (volume_uses_tc(C, vol_dtype))
+        return run_volume_tc(fmap1, fmap2, n_pairs, C, h, w, levels, num_levels, workspace, workspace_bytes, s);
     if (vol_dtype == VFML_F32) return run_volume<float>(fmap1, fmap2, n_pairs, C, h, w, levels, num_levels, to_stream(s));
     return run_volume<__half>(fmap1, fmap2, n_pairs, C, h, w, levels, num_levels, to_stream(s));
 }

@@ -4,9 +4,10 @@
 // CUDA-core bound (225 MACs per output, no shared operand for tensor cores).  A CTA owns an
 // 8 x 16 pixel tile of one image and a group of channels (lane <-> channel, or channel pair for
 // fp16 storage, so every global and shared access is a 128-byte row).  The tile plus its halo and
-// the group's k*k weights are staged in shared memory once; each warp then produces one output
-// row with a register sliding window: 16 outputs x k taps per loaded input value, i.e. ~8 FMAs
-// per shared-memory load.
+// is staged in shared memory once with cp.async (84 KB for k = 15, so two CTAs share an SM and one
+// CTA's staging overlaps the other's math); weights come through L1.  Each warp then produces one
+// output row with a register sliding window: 16 outputs x k taps per loaded input value, i.e.
+// ~8 FMAs per shared-memory load.
 #include "common.cuh"
 
 namespace vfml {
@@ -28,7 +29,7 @@ template <> struct DwVec<__half> {
 };
 
 template <typename T, int K>
-__global__ void __launch_bounds__(DW_TY * 32)
+__global__ void __launch_bounds__(DW_TY * 32, 2)
 dwconv_tile_kernel(const T* __restrict__ x, T* __restrict__ y, int h, int w, int C, int64_t px, int64_t py,
                    const float* __restrict__ wgt, const float* __restrict__ bias, int tiles_x, int tiles_y) {
     using V = DwVec<T>;
@@ -40,7 +41,6 @@ dwconv_tile_kernel(const T* __restrict__ x, T* __restrict__ y, int h, int w, int
 
     extern __shared__ __align__(16) uint8_t dw_smem[];
     ld_t* tile = reinterpret_cast<ld_t*>(dw_smem);                                   // [TWY][TWX][32] of ld_t
-    float* wsm = reinterpret_cast<float*>(dw_smem + (size_t)TWY * TWX * 32 * sizeof(ld_t));   // [K*K][VEC][32]
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int tile_id = blockIdx.x;
@@ -53,22 +53,18 @@ dwconv_tile_kernel(const T* __restrict__ x, T* __restrict__ y, int h, int w, int
     // a lane's channels are valid as a unit when C and the pitch keep the vector aligned (checked by the host)
     const bool ch_ok = c0 < C;
 
-    // ---- stage the input tile (zero outside the image / channel range) and the weights
+    // ---- stage the input tile with asynchronous 4-byte copies (zero-filled outside the image / channel
+    //      range): every copy of the CTA is in flight at once, one wait at the end
     for (int i = warp; i < TWY * TWX; i += DW_TY) {
         const int ty = i / TWX, tx = i - ty * TWX;
         const int gy = y0 + ty - R, gx = x0 + tx - R;
-        float z[VEC];
-#pragma unroll
-        for (int v = 0; v < VEC; ++v) z[v] = 0.0f;
-        ld_t val = V::pack(z);
-        if (ch_ok && gy >= 0 && gy < h && gx >= 0 && gx < w)
-            val = *reinterpret_cast<const ld_t*>(x + (img_row0 + (int64_t)gy * w + gx) * px + c0);
-        tile[i * 32 + lane] = val;
+        const bool ok = ch_ok && gy >= 0 && gy < h && gx >= 0 && gx < w;
+        const T* src = ok ? x + (img_row0 + (int64_t)gy * w + gx) * px + c0 : x;
+        const uint32_t dst = (uint32_t)__cvta_generic_to_shared(tile + i * 32 + lane);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(ok ? 4 : 0) : "memory");
     }
-    for (int i = warp; i < K * K; i += DW_TY) {
-#pragma unroll
-        for (int v = 0; v < VEC; ++v) wsm[(i * VEC + v) * 32 + lane] = (c0 + v < C) ? __ldg(wgt + (int64_t)i * C + c0 + v) : 0.0f;
-    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
 
     // ---- one output row per warp, DW_TX outputs x VEC channels per lane
@@ -84,7 +80,7 @@ dwconv_tile_kernel(const T* __restrict__ x, T* __restrict__ y, int h, int w, int
 #pragma unroll
         for (int kx = 0; kx < K; ++kx)
 #pragma unroll
-            for (int v = 0; v < VEC; ++v) wr[kx][v] = wsm[((ky * K + kx) * VEC + v) * 32 + lane];
+            for (int v = 0; v < VEC; ++v) wr[kx][v] = ch_ok ? __ldg(wgt + (int64_t)(ky * K + kx) * C + c0 + v) : 0.0f;   // L1-resident
         const ld_t* row = tile + (size_t)(warp + ky) * TWX * 32 + lane;
 #pragma unroll
         for (int i = 0; i < TWX; ++i) {
@@ -94,8 +90,16 @@ dwconv_tile_kernel(const T* __restrict__ x, T* __restrict__ y, int h, int w, int
             for (int kx = 0; kx < K; ++kx) {
                 const int o = i - kx;
                 if (o >= 0 && o < DW_TX) {
+                    if constexpr (VEC == 2) {
+                        // both channels of the lane in one packed FFMA2 (fma.rn.f32x2): half the issue slots
+                        asm("{\n.reg .b64 ra, rb, rc;\nmov.b64 ra, {%2, %3};\nmov.b64 rb, {%4, %5};\nmov.b64 rc, {%0, %1};\n"
+                            "fma.rn.f32x2 rc, ra, rb, rc;\nmov.b64 {%0, %1}, rc;\n}"
+                            : "+f"(acc[o][0]), "+f"(acc[o][VEC - 1])
+                            : "f"(wr[kx][0]), "f"(wr[kx][VEC - 1]), "f"(xv[0]), "f"(xv[VEC - 1]));
+                    } else {
 #pragma unroll
-                    for (int v = 0; v < VEC; ++v) acc[o][v] = fmaf(wr[kx][v], xv[v], acc[o][v]);
+                        for (int v = 0; v < VEC; ++v) acc[o][v] = fmaf(wr[kx][v], xv[v], acc[o][v]);
+                    }
                 }
             }
         }
@@ -125,7 +129,7 @@ static int launch_dw_tile(const T* x, T* y, int n_img, int h, int w, int C, int6
                           const float* bias, cudaStream_t st) {
     using V = DwVec<T>;
     constexpr int TWX = DW_TX + K - 1, TWY = DW_TY + K - 1;
-    const size_t smem = (size_t)TWY * TWX * 32 * sizeof(typename V::ld_t) + (size_t)K * K * V::VEC * 32 * sizeof(float);
+    const size_t smem = (size_t)TWY * TWX * 32 * sizeof(typename V::ld_t);
     auto kern = dwconv_tile_kernel<T, K>;
     static bool attr_done = false;
     if (!attr_done) {

@@ -94,6 +94,22 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+__device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+}
+// the registers of an issued tcgen05.ld may only be read after this wait; they are passed through the
+// asm statement so that the compiler cannot hoist their uses above it
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[16]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
+                   "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+                 :: "memory");
+}
+
 // shared-memory matrix descriptor, K-major, 128-byte swizzle: 8-row groups of 128 B rows, 1024 B apart
 __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
     uint64_t d = 0;
@@ -257,103 +273,131 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             float* d32 = reinterpret_cast<float*>(p.D) + bz * p.strideD + (int64_t)m * p.ldd;
             mbar_wait(&acc_full[buf], aph);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            for (int c = hsel * 16; c < BN; c += 32) {
+            // software pipeline over this warp's 16-column chunks: the TMEM load and the residual load of
+            // chunk i+1 are in flight while chunk i goes through the epilogue math and is stored
+            const bool res_vec = has_res && row_ok && ((reinterpret_cast<uintptr_t>(rrow) & 15) == 0) && ((n0 & 7) == 0);
+            const uint32_t trow = tmem_base + buf * 256u + ((uint32_t)(q * 32) << 16);
+            uint32_t tc[16], tn[16];
+            uint4 rc0 = make_uint4(0, 0, 0, 0), rc1 = rc0, rn0 = rc0, rn1 = rc0;
+            int c = hsel * 16;
+            if (c < BN && n0 + c < p.N) {
+                tmem_ld16_issue(trow + (uint32_t)c, tc);
+                if (res_vec && n0 + c + 16 <= p.N) {
+                    rc0 = *reinterpret_cast<const uint4*>(rrow + n0 + c);
+                    rc1 = *reinterpret_cast<const uint4*>(rrow + n0 + c + 8);
+                }
+                tmem_ld_wait(tc);
+            }
+            for (; c < BN; c += 32) {
                 const int n = n0 + c;
                 if (n >= p.N) break;                  // warp-uniform
-                float v[16];
-                tmem_ld16(tmem_base + buf * 256u + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
-                if (!row_ok) continue;
-                const bool full = n + 16 <= p.N;
-                float2 x[8];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) x[i] = mul2(make_float2(v[2 * i], v[2 * i + 1]), alpha2);
-                if (has_bias) {
-                    if (p.vec_in_smem) {
-                        const float4* b4 = reinterpret_cast<const float4*>(s_vec + (n - 0));
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            const float4 b = b4[i];
-                            x[2 * i] = add2(x[2 * i], make_float2(b.x, b.y));
-                            x[2 * i + 1] = add2(x[2 * i + 1], make_float2(b.z, b.w));
-                        }
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 8; ++i)
-                            x[i] = add2(x[i], make_float2(__ldg(p.bias + min(n + 2 * i, p.N - 1)), __ldg(p.bias + min(n + 2 * i + 1, p.N - 1))));
+                const int cn = c + 32;
+                const bool has_next = cn < BN && n0 + cn < p.N;
+                if (has_next) {
+                    tmem_ld16_issue(trow + (uint32_t)cn, tn);
+                    if (res_vec && n0 + cn + 16 <= p.N) {
+                        rn0 = *reinterpret_cast<const uint4*>(rrow + n0 + cn);
+                        rn1 = *reinterpret_cast<const uint4*>(rrow + n0 + cn + 8);
                     }
                 }
-                if (has_res) {
-                    if (full && ((reinterpret_cast<uintptr_t>(rrow + n) & 15) == 0)) {
-                        const uint4 t0 = *reinterpret_cast<const uint4*>(rrow + n);
-                        const uint4 t1 = *reinterpret_cast<const uint4*>(rrow + n + 8);
-                        const __half2* h0 = reinterpret_cast<const __half2*>(&t0);
-                        const __half2* h1 = reinterpret_cast<const __half2*>(&t1);
+                if (row_ok) {
+                    const bool full = n + 16 <= p.N;
+                    float2 x[8];
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            x[i] = add2(x[i], __half22float2(h0[i]));
-                            x[4 + i] = add2(x[4 + i], __half22float2(h1[i]));
-                        }
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 8; ++i)
-                            x[i] = add2(x[i], make_float2(n + 2 * i < p.N ? __half2float(rrow[n + 2 * i]) : 0.0f,
-                                                          n + 2 * i + 1 < p.N ? __half2float(rrow[n + 2 * i + 1]) : 0.0f));
-                    }
-                }
-                if (do_gelu) {
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) x[i] = gelu_poly2(x[i]);
-                }
-                if (do_relu) {
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) x[i] = make_float2(fmaxf(x[i].x, 0.0f), fmaxf(x[i].y, 0.0f));
-                }
-                if (has_dw) {   // k = 1 depthwise stage: gelu(v + (w * v + b))
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        float2 w2, b2;
+                    for (int i = 0; i < 8; ++i) x[i] = mul2(make_float2(__uint_as_float(tc[2 * i]), __uint_as_float(tc[2 * i + 1])), alpha2);
+                    if (has_bias) {
                         if (p.vec_in_smem) {
-                            w2 = *reinterpret_cast<const float2*>(s_vec + vec_cols + n + 2 * i);
-                            b2 = *reinterpret_cast<const float2*>(s_vec + 2 * vec_cols + n + 2 * i);
+                            const float4* b4 = reinterpret_cast<const float4*>(s_vec + n);
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                const float4 b = b4[i];
+                                x[2 * i] = add2(x[2 * i], make_float2(b.x, b.y));
+                                x[2 * i + 1] = add2(x[2 * i + 1], make_float2(b.z, b.w));
+                            }
                         } else {
-                            const int n1 = min(n + 2 * i, p.N - 1), n2 = min(n + 2 * i + 1, p.N - 1);
-                            w2 = make_float2(__ldg(p.dw_w + n1), __ldg(p.dw_w + n2));
-                            b2 = make_float2(__ldg(p.dw_b + n1), __ldg(p.dw_b + n2));
+#pragma unroll
+                            for (int i = 0; i < 8; ++i)
+                                x[i] = add2(x[i], make_float2(__ldg(p.bias + min(n + 2 * i, p.N - 1)), __ldg(p.bias + min(n + 2 * i + 1, p.N - 1))));
                         }
-                        x[i] = gelu_poly2(add2(x[i], fma2(w2, x[i], b2)));
+                    }
+                    if (has_res) {
+                        if (res_vec && full) {
+                            const __half2* h0 = reinterpret_cast<const __half2*>(&rc0);
+                            const __half2* h1 = reinterpret_cast<const __half2*>(&rc1);
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                x[i] = add2(x[i], __half22float2(h0[i]));
+                                x[4 + i] = add2(x[4 + i], __half22float2(h1[i]));
+                            }
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i)
+                                x[i] = add2(x[i], make_float2(n + 2 * i < p.N ? __half2float(rrow[n + 2 * i]) : 0.0f,
+                                                              n + 2 * i + 1 < p.N ? __half2float(rrow[n + 2 * i + 1]) : 0.0f));
+                        }
+                    }
+                    if (do_gelu) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) x[i] = gelu_poly2(x[i]);
+                    }
+                    if (do_relu) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) x[i] = make_float2(fmaxf(x[i].x, 0.0f), fmaxf(x[i].y, 0.0f));
+                    }
+                    if (has_dw) {   // k = 1 depthwise stage: gelu(v + (w * v + b))
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            float2 w2, b2;
+                            if (p.vec_in_smem) {
+                                w2 = *reinterpret_cast<const float2*>(s_vec + vec_cols + n + 2 * i);
+                                b2 = *reinterpret_cast<const float2*>(s_vec + 2 * vec_cols + n + 2 * i);
+                            } else {
+                                const int n1 = min(n + 2 * i, p.N - 1), n2 = min(n + 2 * i + 1, p.N - 1);
+                                w2 = make_float2(__ldg(p.dw_w + n1), __ldg(p.dw_w + n2));
+                                b2 = make_float2(__ldg(p.dw_b + n1), __ldg(p.dw_b + n2));
+                            }
+                            x[i] = gelu_poly2(add2(x[i], fma2(w2, x[i], b2)));
+                        }
+                    }
+                    if (p.out_f32) {
+                        if (full && ((reinterpret_cast<uintptr_t>(d32 + n) & 15) == 0)) {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i)
+                                *reinterpret_cast<float4*>(d32 + n + 4 * i) = make_float4(x[2 * i].x, x[2 * i].y, x[2 * i + 1].x, x[2 * i + 1].y);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                if (n + 2 * i < p.N) d32[n + 2 * i] = x[i].x;
+                                if (n + 2 * i + 1 < p.N) d32[n + 2 * i + 1] = x[i].y;
+                            }
+                        }
+                    } else {
+                        if (full && ((reinterpret_cast<uintptr_t>(d16 + n) & 15) == 0)) {
+                            uint4 o0, o1;
+                            __half2* h0 = reinterpret_cast<__half2*>(&o0);
+                            __half2* h1 = reinterpret_cast<__half2*>(&o1);
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                h0[i] = __float22half2_rn(x[i]);
+                                h1[i] = __float22half2_rn(x[4 + i]);
+                            }
+                            *reinterpret_cast<uint4*>(d16 + n) = o0;
+                            *reinterpret_cast<uint4*>(d16 + n + 8) = o1;
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                if (n + 2 * i < p.N) d16[n + 2 * i] = __float2half_rn(x[i].x);
+                                if (n + 2 * i + 1 < p.N) d16[n + 2 * i + 1] = __float2half_rn(x[i].y);
+                            }
+                        }
                     }
                 }
-                if (p.out_f32) {
-                    if (full && ((reinterpret_cast<uintptr_t>(d32 + n) & 15) == 0)) {
+                if (has_next) {
+                    tmem_ld_wait(tn);
 #pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            *reinterpret_cast<float4*>(d32 + n + 4 * i) = make_float4(x[2 * i].x, x[2 * i].y, x[2 * i + 1].x, x[2 * i + 1].y);
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            if (n + 2 * i < p.N) d32[n + 2 * i] = x[i].x;
-                            if (n + 2 * i + 1 < p.N) d32[n + 2 * i + 1] = x[i].y;
-                        }
-                    }
-                } else {
-                    if (full && ((reinterpret_cast<uintptr_t>(d16 + n) & 15) == 0)) {
-                        uint4 o0, o1;
-                        __half2* h0 = reinterpret_cast<__half2*>(&o0);
-                        __half2* h1 = reinterpret_cast<__half2*>(&o1);
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            h0[i] = __float22half2_rn(x[i]);
-                            h1[i] = __float22half2_rn(x[4 + i]);
-                        }
-                        *reinterpret_cast<uint4*>(d16 + n) = o0;
-                        *reinterpret_cast<uint4*>(d16 + n + 8) = o1;
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            if (n + 2 * i < p.N) d16[n + 2 * i] = __float2half_rn(x[i].x);
-                            if (n + 2 * i + 1 < p.N) d16[n + 2 * i + 1] = __float2half_rn(x[i].y);
-                        }
-                    }
+                    for (int i = 0; i < 16; ++i) tc[i] = tn[i];
+                    rc0 = rn0;
+                    rc1 = rn1;
                 }
             }
             // this warp is done reading the accumulator: hand it back to the MMA warp

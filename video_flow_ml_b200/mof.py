@@ -61,7 +61,7 @@ class _PCWeights:
 class MOFEngine:
     """Stateless-per-window MOF refinement; buffers are cached per (F, h, w)."""
 
-    def __init__(self, state_dict, device, dtype=torch.float32, iters=ITERS, ops=None, encoder_dtype=None):
+    def __init__(self, state_dict, device, dtype=torch.float32, iters=ITERS, ops=None, encoder_dtype=None, use_graph=True):
         self.ops = ops or _ops
         self.dev = torch.device(device)
         self.dt = dtype
@@ -91,6 +91,7 @@ class MOFEngine:
         self.fnet = TwinsStage01(sd, "fnet.svt", dev, enc_dt) if "fnet.svt.patch_embeds.0.proj.weight" in sd else None
         self.cnet = TwinsStage01(sd, "cnet.svt", dev, enc_dt) if "cnet.svt.patch_embeds.0.proj.weight" in sd else None
         self._ws = {}
+        self.use_graph = use_graph
 
     # ------------------------------------------------------------------ buffers
     def _rows_buf(self, n, c, dtype=None):
@@ -227,6 +228,44 @@ class MOFEngine:
         o.gemm(m256, self.w_m2[chan], mask, bias=self.b_m2_x100[chan].contiguous(), alpha=100.0)
         return mask
 
+    def _iterations_body(self, ws, fmaps, net, inp, Fc, h, w):
+        """pyramids, attention, `iters` update steps.  Leaves net in x512[:, 0:128]; returns the coords."""
+        o = self.ops
+        P = h * w
+        fpyr, bpyr = self.build_pyramids(fmaps)
+        x512 = ws["x512"]
+        o.nchw_to_rows(net, x512[:, 0:128])
+        o.nchw_to_rows(inp, x512[:, 128:256])
+        o.rows_fill(ws["x400"][:, 352:400], self.init_mhs)          # init_hidden_state, stack.py:72-73
+        self.attention(ws, Fc, P)
+        fc = o.coords_grid(Fc, h, w, self.dev)
+        bc = o.coords_grid(Fc, h, w, self.dev)
+        for _ in range(self.iters):
+            self.update_step(ws, fpyr, bpyr, fc, bc, Fc, h, w)
+        return fc, bc
+
+    def _run_iterations(self, ws, fmaps, net, inp, Fc, h, w):
+        """The ~1300 launches of a window are captured once per shape into a CUDA graph and replayed
+        (inputs are copied into static buffers; the graph owns the pyramids and the coords)."""
+        fmaps, net, inp = fmaps.float().contiguous(), net.float().contiguous(), inp.float().contiguous()
+        if not (self.use_graph and fmaps.is_cuda):
+            return self._iterations_body(ws, fmaps, net, inp, Fc, h, w)
+        g = ws.get("graph")
+        if g is None or g["iters"] != self.iters:
+            static = [torch.empty_like(t) for t in (fmaps, net, inp)]
+            for s_, t in zip(static, (fmaps, net, inp)):
+                s_.copy_(t)
+            self._iterations_body(ws, *static, Fc, h, w)            # eager warm-up: one-time kernel attributes
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                coords = self._iterations_body(ws, *static, Fc, h, w)
+            g = ws["graph"] = {"graph": graph, "static": static, "coords": coords, "iters": self.iters}
+        for s_, t in zip(g["static"], (fmaps, net, inp)):
+            s_.copy_(t)
+        g["graph"].replay()
+        return g["coords"]
+
     # ------------------------------------------------------------------ forward
     @torch.no_grad()
     def refine(self, fmaps, net, inp, select=None, crop=None, out=None):
@@ -237,17 +276,7 @@ class MOFEngine:
         T, _, h, w = fmaps.shape
         Fc, P = T - 2, h * w
         ws = self._workspace(Fc, h, w)
-        fpyr, bpyr = self.build_pyramids(fmaps.float())
-        x512 = ws["x512"]
-        o.nchw_to_rows(net.float().contiguous(), x512[:, 0:128])
-        o.nchw_to_rows(inp.float().contiguous(), x512[:, 128:256])
-        o.rows_fill(ws["x400"][:, 352:400], self.init_mhs)          # init_hidden_state, stack.py:72-73
-        self.attention(ws, Fc, P)
-        fc = o.coords_grid(Fc, h, w, self.dev)
-        bc = o.coords_grid(Fc, h, w, self.dev)
-        for _ in range(self.iters):
-            self.update_step(ws, fpyr, bpyr, fc, bc, Fc, h, w)
-        del fpyr, bpyr
+        fc, bc = self._run_iterations(ws, fmaps, net, inp, Fc, h, w)
         if select is None:
             flows = torch.empty((1, 2 * Fc, 2, 8 * h, 8 * w), dtype=torch.float32, device=self.dev)
             mk = self.mask_rows(ws, slice(0, Fc), h, w, slice(0, 576))
