@@ -51,6 +51,10 @@ int vfml_version(void);
 const char* vfml_last_error(void);
 /* Number of kernels this library has launched since it was loaded (all threads). */
 uint64_t vfml_launch_count(void);
+/* Device-wide hint (cudaLimitMaxL2FetchGranularity) for the current device: 32, 64 or 128 bytes
+ * fetched from DRAM per L2 sector miss.  The tiled correlation lookup gathers single 32-byte
+ * sectors, so the engine asks for 32; streaming kernels are unaffected (they use whole lines). */
+int vfml_set_l2_fetch_granularity(int bytes);
 
 /* ---------------------------------------------------------------------------------
  * Layout conversion.  src [n, c, hw] fp32 planar  <->  rows [n*hw, pitch] of `dtype`.
@@ -97,6 +101,39 @@ int vfml_corr_lookup_pair(const void* const* levels_fwd, const void* const* leve
                           int vol_dtype, int n_frames, int h, int w, const float* coords_fwd,
                           const float* coords_bwd, void* out_fwd, void* out_bwd, int out_pitch,
                           int out_col, int out_dtype, vfml_stream_t s);
+
+/* ---------------------------------------------------------------------------------
+ * Gather-friendly ("tiled") fp16 pyramid + lookup: the engine's layout of the same data.
+ * Replaces the same reference code as vfml_corr_volume_pyramid / vfml_corr_lookup
+ * (MOFNetStack/corr.py:59-97, core/utils/utils.py:62-76).
+ *
+ * Level l of source pixel q is a slab of vfml_corr_tiled_slab_bytes(h, w, l) bytes:
+ * NTX x NTY tiles (NTX = ceil(w_l/4), NTY = ceil(h_l/4)), tile (tx, ty) at byte
+ * (tx*NTY + ty)*32; a tile holds 4 x 4 fp16 texels x-major: element [xr][yy] is texel
+ * (4tx+xr, 4ty+yy) of the level, zero beyond the level.  levels[l] is [n_rows] slabs.
+ *
+ * vfml_corr_tile_pyramid  : vol0 [rows, h*w] fp16 (row-major level 0) -> the tiled levels
+ *                           (levels 1.. are 2x2 averages of the previous fp16 level).
+ * vfml_corr_volume_pyramid_tiled : fmaps [n_pairs, C, h, w] fp32 -> tiled levels, C % 8 == 0,
+ *                           workspace of vfml_corr_volume_tiled_workspace() bytes.
+ * vfml_corr_lookup_tiled  : radius 4, 4 levels, one or two sets (levels_b may be NULL) in one
+ *                           launch; out_* are fp16 rows buffers [n_frames*h*w, out_pitch],
+ *                           out_pitch % 8 == 0, out_col % 8 == 0, 16-byte aligned.  Channel
+ *                           order is the PERMUTED one:  tap (level l, x offset i, y offset j)
+ *                           of the reference's channel l*81 + i*9 + j is written to
+ *                           column (l*9+i)*8 + j for j < 8 and 288 + l*9 + i for j == 8.
+ *                           math_f32 != 0 interpolates in fp32 (one rounding), else in fp16x2.
+ * ------------------------------------------------------------------------------- */
+size_t vfml_corr_tiled_slab_bytes(int h, int w, int level);
+int vfml_corr_tile_pyramid(const void* vol0, int64_t rows, int h, int w, void* const* levels,
+                           int num_levels, vfml_stream_t s);
+size_t vfml_corr_volume_tiled_workspace(int n_pairs, int C, int h, int w);
+int vfml_corr_volume_pyramid_tiled(const float* fmap1, const float* fmap2, int n_pairs, int C, int h,
+                                   int w, void* const* levels, int num_levels, void* workspace,
+                                   size_t workspace_bytes, vfml_stream_t s);
+int vfml_corr_lookup_tiled(const void* const* levels_a, const void* const* levels_b, int n_frames,
+                           int h, int w, const float* coords_a, const float* coords_b, void* out_a,
+                           void* out_b, int out_pitch, int out_col, int math_f32, vfml_stream_t s);
 
 /* ---------------------------------------------------------------------------------
  * Convex 8x upsampling (softmax over 9 taps fused).

@@ -58,6 +58,27 @@ def corr_lookup_pair(levels_f, levels_b, coords_f, coords_b, out_f, out_b):
     corr_lookup(levels_b, coords_b, 4, out=out_b)
 
 
+def corr_lookup_perm(device=None):
+    from video_flow_ml_b200.ops import corr_lookup_perm as real      # pure index arithmetic, no library call
+    return real(device)
+
+
+def corr_volume_pyramid_tiled(f1, f2, workspace=None):
+    return corr_volume_pyramid(f1, f2, 4)
+
+
+def corr_lookup_tiled(pyr_a, pyr_b, coords_a, coords_b, out_a, out_b, math_f32=False):
+    """Same taps as corr_lookup, written in the tiled kernel's permuted channel order."""
+    perm = corr_lookup_perm()
+    for pyr, c, out in ((pyr_a, coords_a, out_a), (pyr_b, coords_b, out_b)):
+        if pyr is None:
+            continue
+        tmp = torch.empty(out.shape, dtype=torch.float32)
+        corr_lookup(pyr, c, 4, out=tmp)
+        out.copy_(tmp[:, perm].to(out.dtype))
+    return out_a, out_b
+
+
 def convex_upsample8(flow, mask, out=None, crop=None, flow_is_coords=False):
     n, _, h, w = flow.shape
     if flow_is_coords:

@@ -34,3 +34,17 @@ def test_engine_dataflow_matches_oracle(mof_weights):
     assert (got - want).abs().max() < 2e-3, (got - want).abs().max()
     sel = eng.refine(of, on, oi, select=3, crop=(2, 1, 120, 180))
     assert (sel - want[0, 3, :, 2:122, 1:181]).abs().max() < 2e-3
+
+
+def test_engine_tiled_lookup_channel_permutation(mof_weights):
+    """The tiled lookup emits the 324 correlation channels in a permuted order; the engine folds the
+    permutation into the convc1 weights.  Result must equal the unpermuted path."""
+    frames = cases.mof_case()
+    win = omof.pad_frames(omof.frames_to_window(frames, 2, 5)).contiguous()
+    of, on, oi = omof.mof_encode(win, mof_weights)
+    ref = MOFEngine(mof_weights, "cpu", torch.float32, iters=2, ops=fake_ops, tiled=False).refine(of, on, oi)
+    got = MOFEngine(mof_weights, "cpu", torch.float32, iters=2, ops=fake_ops, tiled=True).refine(of, on, oi)
+    assert (got - ref).abs().max() < 1e-3, (got - ref).abs().max()      # fp32 summation order differs
+    perm = fake_ops.corr_lookup_perm()
+    assert sorted(perm.tolist()) == list(range(324))
+    assert perm[0] == 0 and perm[7] == 7 and perm[8] == 9 and perm[288] == 8 and perm[323] == 3 * 81 + 8 * 9 + 8

@@ -314,3 +314,63 @@ def test_corrblock_dropin(ops, golden):
     assert len(blk.corr_pyramid) == 4 and blk.corr_pyramid[0].shape == (768, 1, 16, 24)
     close(blk(cu(coords)), T(g["lookup"]), 5e-5)
     close(CorrBlock.corr(cu(f1), cu(f2))[0, :2], T(g["vol0"]), 2e-5)
+
+
+# ---------------------------------------------------------------- tiled (gather-friendly) pyramid + lookup
+def _tiled_case(ops, n, h, w, seed, spread=6.0):
+    r = np.random.default_rng(seed)
+    f1 = r.standard_normal((n, 64, h, w)).astype(np.float32)
+    f2 = r.standard_normal((n, 64, h, w)).astype(np.float32)
+    coords = omof.pixel_grid(n, h, w) + T((spread * r.standard_normal((n, 2, h, w))).astype(np.float32))
+    # edge cases of the reference sampler: far out of range on both sides, exact integers, NaN
+    flat = coords.view(n, 2, -1)
+    flat[0, 0, 0], flat[0, 1, 1] = -1.0e9, 1.0e9
+    flat[0, :, 2] = 3.0
+    flat[0, 0, 3] = float("nan")
+    flat[0, :, 4] = torch.tensor([w - 1.0, h - 1.0])
+    flat[0, :, 5] = torch.tensor([-4.5, -3.25])
+    flat[0, :, 6] = torch.tensor([w + 3.75, h + 2.5])
+    return f1, f2, coords
+
+
+@pytest.mark.parametrize("n,h,w", [(1, 16, 24), (3, 20, 31), (2, 47, 39), (1, 16, 16)])
+@pytest.mark.parametrize("math_f32", [True, False])
+def test_tiled_lookup_matches_oracle(ops, n, h, w, math_f32):
+    f1, f2, coords = _tiled_case(ops, n, h, w, 11)
+    pyr16 = ops.corr_volume_pyramid(cu(f1), cu(f2), 4, torch.float16)                 # row-major fp16 pyramid
+    tp = ops.corr_tile_pyramid(pyr16[0].view(n * h * w, h * w), h, w)
+    want = torch.zeros((n * h * w, 324), dtype=torch.float32, device="cuda")
+    c = cu(coords)
+    ops.corr_lookup(pyr16, c, 4, out=want)                                            # fp32 interpolation of the same fp16 texels
+    got = rows_buf(n * h * w, 324, torch.float16, pad=4)
+    ops.corr_lookup_tiled(tp, None, c, None, got, None, math_f32=math_f32)
+    perm = ops.corr_lookup_perm("cuda")
+    unperm = torch.empty_like(want)
+    unperm[:, perm] = got.float()
+    scale = want.abs().max().item()
+    # fp32 math: one rounding to fp16 (2^-11 relative); fp16x2 math: three roundings
+    tol = (1.0 if math_f32 else 3.0) * 2.0 ** -11 * scale + 1e-6
+    err = (unperm - want).abs().max().item()
+    assert err <= tol, f"max err {err:.3e} > {tol:.3e}"
+    # and against the CPU oracle on fp32 volumes (fp16 storage error of the volume included)
+    want_o = omof.corr_lookup(omof.corr_pyramid(T(f1), T(f2)), coords.nan_to_num(nan=-1.0e6))
+    close(unperm.view(n, h, w, 324).permute(0, 3, 1, 2), want_o, 4.0 * 2.0 ** -11 * scale + 1e-6)
+
+
+def test_tiled_volume_pair_launch(ops):
+    """fmaps -> tiled pyramid in one call; both directions in one launch equal two single launches."""
+    n, h, w = 2, 24, 40
+    f1, f2, ca = _tiled_case(ops, n, h, w, 3)
+    _, f3, cb = _tiled_case(ops, n, h, w, 4)
+    ta = ops.corr_volume_pyramid_tiled(cu(f1), cu(f2))
+    tb = ops.corr_volume_pyramid_tiled(cu(f1), cu(f3))
+    pyr16 = ops.corr_volume_pyramid(cu(f1), cu(f2), 4, torch.float16)
+    ref = ops.corr_tile_pyramid(pyr16[0].view(n * h * w, h * w), h, w)
+    for a, b in zip(ta.levels, ref.levels):
+        assert torch.equal(a, b)
+    oa, ob = rows_buf(n * h * w, 324, torch.float16, 4), rows_buf(n * h * w, 324, torch.float16, 4)
+    ops.corr_lookup_tiled(ta, tb, cu(ca), cu(cb), oa, ob)
+    sa, sb = rows_buf(n * h * w, 324, torch.float16, 4), rows_buf(n * h * w, 324, torch.float16, 4)
+    ops.corr_lookup_tiled(ta, None, cu(ca), None, sa, None)
+    ops.corr_lookup_tiled(tb, None, cu(cb), None, sb, None)
+    assert torch.equal(oa, sa) and torch.equal(ob, sb)

@@ -27,12 +27,18 @@ PROTOTYPES = {
     "vfml_version": (i32, []),
     "vfml_last_error": (C.c_char_p, []),
     "vfml_launch_count": (C.c_uint64, []),
+    "vfml_set_l2_fetch_granularity": (i32, [i32]),
     "vfml_nchw_to_rows": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp]),
     "vfml_rows_to_nchw": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp]),
     "vfml_corr_volume_workspace": (sz, [i32, i32, i32, i32, i32]),
     "vfml_corr_volume_pyramid": (i32, [vp, vp, i32, i32, i32, i32, C.POINTER(vp), i32, i32, vp, sz, vp]),
     "vfml_corr_lookup": (i32, [C.POINTER(vp), i32, i32, i32, i32, i32, i32, vp, vp, i32, i32, i32, i32, vp]),
     "vfml_corr_lookup_pair": (i32, [C.POINTER(vp), C.POINTER(vp), i32, i32, i32, i32, i32, vp, vp, vp, vp, i32, i32, i32, vp]),
+    "vfml_corr_tiled_slab_bytes": (sz, [i32, i32, i32]),
+    "vfml_corr_tile_pyramid": (i32, [vp, i64, i32, i32, C.POINTER(vp), i32, vp]),
+    "vfml_corr_volume_tiled_workspace": (sz, [i32, i32, i32, i32]),
+    "vfml_corr_volume_pyramid_tiled": (i32, [vp, vp, i32, i32, i32, i32, C.POINTER(vp), i32, vp, sz, vp]),
+    "vfml_corr_lookup_tiled": (i32, [C.POINTER(vp), C.POINTER(vp), i32, i32, i32, vp, vp, vp, vp, i32, i32, i32, vp]),
     "vfml_convex_upsample8": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, i64, i64, i64, i32, i32, i32, i32, i32, vp]),
     "vfml_encode_gamedev": (i32, [vp, vp, i32, i32, f32, f32, f32, f32, vp]),
     "vfml_encode_mv_rg8": (i32, [vp, vp, i32, i32, f32, vp]),

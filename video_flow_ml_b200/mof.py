@@ -17,6 +17,7 @@ this part under fp16 autocast, network.py:149-192).
 """
 import torch
 
+from . import _lib
 from . import ops as _ops
 from .twins import TwinsStage01
 
@@ -40,20 +41,26 @@ def _pad_k(w):
 class _PCWeights:
     """PCBlock4_Deep_nopool_res parameters (stack.py:8-32) prepacked for the kernels."""
 
-    def __init__(self, sd, p, k, dev, dt):
+    def __init__(self, sd, p, k, dev, dt, perm=None):
+        """perm (optional, LongTensor [Cin]): the block's input arrives with channel `new` holding the
+        reference's channel perm[new]; every op of the block up to ffn2 is channel-wise or a 1x1
+        convolution, so the permutation is folded into the weights once and costs nothing at run time."""
         g = lambda n: sd[f"{p}.{n}"].to(dev)
-        mat = lambda n: _pad_k(g(n + ".weight").flatten(1).to(dt))
-        vec = lambda n: g(n + ".bias").float().contiguous()
+        ident = lambda t: t
+        pin = ident if perm is None else (lambda t: t.index_select(t.dim() - 1, perm.to(t.device)))   # input-channel axis (last)
+        pout = ident if perm is None else (lambda t: t.index_select(0, perm.to(t.device)))            # output-channel axis (first)
+        mat = lambda n, f=ident: _pad_k(f(g(n + ".weight").flatten(1)).to(dt))
+        vec = lambda n, f=ident: f(g(n + ".bias").float()).contiguous()
         self.k = k
-        self.w1a, self.b1a = mat("ffn1.0"), vec("ffn1.0")
-        self.w1b, self.b1b = mat("ffn1.2"), vec("ffn1.2")
-        self.dw1_w = g("conv_list.0.weight").float().flatten().contiguous()      # k = 1 depthwise
-        self.dw1_b = vec("conv_list.0")
+        self.w1a, self.b1a = mat("ffn1.0", pin), vec("ffn1.0")
+        self.w1b, self.b1b = mat("ffn1.2", pout), vec("ffn1.2", pout)
+        self.dw1_w = pout(g("conv_list.0.weight").float().flatten()).contiguous()      # k = 1 depthwise
+        self.dw1_b = vec("conv_list.0", pout)
         C = self.dw1_w.numel()
-        self.dwk_w = g("conv_list.1.weight").float().reshape(C, k * k).t().contiguous()   # tap-major [k*k, C]
-        self.dwk_b = vec("conv_list.1")
-        self.wpw, self.bpw = mat("pw"), vec("pw")
-        self.w2a, self.b2a = mat("ffn2.0"), vec("ffn2.0")
+        self.dwk_w = pout(g("conv_list.1.weight").float().reshape(C, k * k)).t().contiguous()   # tap-major [k*k, C]
+        self.dwk_b = vec("conv_list.1", pout)
+        self.wpw, self.bpw = mat("pw", lambda t: pin(pout(t))), vec("pw", pout)
+        self.w2a, self.b2a = mat("ffn2.0", pin), vec("ffn2.0")
         self.w2b, self.b2b = mat("ffn2.2"), vec("ffn2.2")
         self.cin, self.hid, self.cout = C, self.w1a.shape[0], self.w2b.shape[0]
 
@@ -61,7 +68,8 @@ class _PCWeights:
 class MOFEngine:
     """Stateless-per-window MOF refinement; buffers are cached per (F, h, w)."""
 
-    def __init__(self, state_dict, device, dtype=torch.float32, iters=ITERS, ops=None, encoder_dtype=None, use_graph=True):
+    def __init__(self, state_dict, device, dtype=torch.float32, iters=ITERS, ops=None, encoder_dtype=None, use_graph=True,
+                 tiled=None):
         self.ops = ops or _ops
         self.dev = torch.device(device)
         self.dt = dtype
@@ -69,7 +77,9 @@ class MOFEngine:
         sd = {k[7:] if k.startswith("module.") else k: v for k, v in state_dict.items()}
         dev, dt = self.dev, dtype
         e = "update_block.encoder"
-        self.convc1 = _PCWeights(sd, e + ".convc1", 15, dev, dt)
+        # fp16 tier: the correlation features come from the tiled lookup in its permuted channel order
+        self.tiled = (dtype == torch.float16) if tiled is None else bool(tiled)
+        self.convc1 = _PCWeights(sd, e + ".convc1", 15, dev, dt, perm=self.ops.corr_lookup_perm() if self.tiled else None)
         self.convc2 = _PCWeights(sd, e + ".convc2", 15, dev, dt)
         self.convf2 = _PCWeights(sd, e + ".convf2", 15, dev, dt)
         self.conv = _PCWeights(sd, e + ".conv", 15, dev, dt)
@@ -92,6 +102,8 @@ class MOFEngine:
         self.cnet = TwinsStage01(sd, "cnet.svt", dev, enc_dt) if "cnet.svt.patch_embeds.0.proj.weight" in sd else None
         self._ws = {}
         self.use_graph = use_graph
+        self.lookup_math_f32 = False     # fp16x2 interpolation: 2.43e-2 px vs 2.37e-2 px (fp32) end to end, 8 % faster
+        self.graph_launches = 0          # kernels executed through CUDA-graph replays (not seen by vfml_launch_count)
 
     # ------------------------------------------------------------------ buffers
     def _rows_buf(self, n, c, dtype=None):
@@ -167,6 +179,9 @@ class MOFEngine:
         """Forward (frames 1..T-2 vs 2..T-1) and backward (vs 0..T-3) pyramids, network.py:157-158."""
         T = fmaps.shape[0]
         c = fmaps[1:T - 1].contiguous()
+        if self.tiled:
+            return (self.ops.corr_volume_pyramid_tiled(c, fmaps[2:T].contiguous()),
+                    self.ops.corr_volume_pyramid_tiled(c, fmaps[0:T - 2].contiguous()))
         fw = self.ops.corr_volume_pyramid(c, fmaps[2:T].contiguous(), CORR_LEVELS, self.dt)
         bw = self.ops.corr_volume_pyramid(c, fmaps[0:T - 2].contiguous(), CORR_LEVELS, self.dt)
         return fw, bw
@@ -188,7 +203,10 @@ class MOFEngine:
         P = h * w
         Np = Fc * P
         corr2, x400, x512 = ws["corr2"], ws["x400"], ws["x512"]
-        o.corr_lookup_pair(fpyr, bpyr, fc, bc, corr2[:Np], corr2[Np:])
+        if self.tiled:
+            o.corr_lookup_tiled(fpyr, bpyr, fc, bc, corr2[:Np], corr2[Np:], math_f32=self.lookup_math_f32)
+        else:
+            o.corr_lookup_pair(fpyr, bpyr, fc, bc, corr2[:Np], corr2[Np:])
         mf = x512[:, 256:384]
         o.motion_glue(fc, bc, x400, ws["f128"], mf, self.convf1_w, self.convf1_b, Fc, h, w)
         full = slice(None)
@@ -258,12 +276,15 @@ class MOFEngine:
             self._iterations_body(ws, *static, Fc, h, w)            # eager warm-up: one-time kernel attributes
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
+            n0 = _lib.launch_count()
             with torch.cuda.graph(graph):
                 coords = self._iterations_body(ws, *static, Fc, h, w)
-            g = ws["graph"] = {"graph": graph, "static": static, "coords": coords, "iters": self.iters}
+            g = ws["graph"] = {"graph": graph, "static": static, "coords": coords, "iters": self.iters,
+                               "launches": _lib.launch_count() - n0}
         for s_, t in zip(g["static"], (fmaps, net, inp)):
             s_.copy_(t)
         g["graph"].replay()
+        self.graph_launches += g["launches"]
         return g["coords"]
 
     # ------------------------------------------------------------------ forward

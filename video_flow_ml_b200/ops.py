@@ -140,6 +140,87 @@ def corr_lookup_pair(levels_f, levels_b, coords_f, coords_b, out_f, out_b):
                                                  _p(out_b), out_f.stride(0), 0, _dt(out_f), _stream()), "corr_lookup_pair")
 
 
+class TiledPyramid:
+    """The engine's gather-friendly fp16 pyramid (include/vfml.h, "tiled" layout): per level a uint8
+    buffer of [n*h*w] slabs of 4x4-texel (32-byte) tiles."""
+
+    def __init__(self, levels, n, h, w):
+        self.levels, self.n, self.h, self.w = levels, n, h, w
+
+
+def corr_lookup_perm(device=None):
+    """perm[new] = old: column `new` of the tiled lookup holds the reference's channel `old`
+    (l*81 + i*9 + j); new = (l*9+i)*8 + j for j < 8, 288 + l*9 + i for j == 8."""
+    perm = torch.empty(324, dtype=torch.long)
+    for l in range(4):
+        for i in range(9):
+            for j in range(9):
+                new = (l * 9 + i) * 8 + j if j < 8 else 288 + l * 9 + i
+                perm[new] = l * 81 + i * 9 + j
+    return perm.to(device) if device is not None else perm
+
+
+def _tiled_levels(n_rows, h, w, device):
+    lib = _lib.load()
+    return [torch.empty((n_rows, lib.vfml_corr_tiled_slab_bytes(h, w, l)), dtype=torch.uint8, device=device) for l in range(4)]
+
+
+def corr_tile_pyramid(vol0, h, w):
+    """vol0 [rows, h*w] fp16 (row-major level-0 volume) -> TiledPyramid with `rows` source pixels."""
+    _cuda(vol0)
+    if vol0.dtype != torch.float16 or not vol0.is_contiguous() or vol0.dim() != 2 or vol0.shape[1] != h * w:
+        raise ValueError("corr_tile_pyramid: vol0 must be a contiguous fp16 [rows, h*w] tensor")
+    if h < 8 or w < 8:
+        raise ValueError(f"corr_tile_pyramid: {h}x{w} is too small for 4 levels")
+    rows = vol0.shape[0]
+    levels = _tiled_levels(rows, h, w, vol0.device)
+    arr = (C.c_void_p * 4)(*[l.data_ptr() for l in levels])
+    _lib.check(_lib.load().vfml_corr_tile_pyramid(_p(vol0), rows, h, w, arr, 4, _stream()), "corr_tile_pyramid")
+    return TiledPyramid(levels, rows // (h * w), h, w)
+
+
+def corr_volume_pyramid_tiled(fmap1, fmap2, workspace=None):
+    """fmaps [n, C, h, w] fp32 -> TiledPyramid (tcgen05 GEMM + fused pool/tile pass)."""
+    _cuda(fmap1, fmap2)
+    _f32c(fmap1, "fmap1"); _f32c(fmap2, "fmap2")
+    if fmap1.shape != fmap2.shape or fmap1.dim() != 4:
+        raise ValueError("corr_volume_pyramid_tiled: fmaps must be [n, C, h, w] of equal shape")
+    n, Cc, h, w = fmap1.shape
+    if h < 8 or w < 8:
+        raise ValueError(f"corr_volume_pyramid_tiled: {h}x{w} is too small for 4 levels")
+    lib = _lib.load()
+    levels = _tiled_levels(n * h * w, h, w, fmap1.device)
+    arr = (C.c_void_p * 4)(*[l.data_ptr() for l in levels])
+    ws_bytes = lib.vfml_corr_volume_tiled_workspace(n, Cc, h, w)
+    if workspace is None or workspace.numel() < ws_bytes:
+        workspace = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=fmap1.device)
+    _lib.check(lib.vfml_corr_volume_pyramid_tiled(_p(fmap1), _p(fmap2), n, Cc, h, w, arr, 4, _p(workspace), workspace.numel(),
+                                                  _stream()), "corr_volume_pyramid_tiled")
+    return TiledPyramid(levels, n, h, w)
+
+
+def corr_lookup_tiled(pyr_a, pyr_b, coords_a, coords_b, out_a, out_b, math_f32=False):
+    """Radius-4 lookups on tiled pyramids, one launch for both sets (pyr_b may be None).
+    out_*: fp16 rows views [n*h*w, 324] in the PERMUTED channel order (corr_lookup_perm)."""
+    _cuda(coords_a, out_a, *pyr_a.levels)
+    _f32c(coords_a, "coords_a"); _rows(out_a, "out_a")
+    n, _, h, w = coords_a.shape
+    if (pyr_a.n, pyr_a.h, pyr_a.w) != (n, h, w) or out_a.shape != (n * h * w, 324) or out_a.dtype != torch.float16:
+        raise ValueError("corr_lookup_tiled: shape mismatch")
+    aa = (C.c_void_p * 4)(*[l.data_ptr() for l in pyr_a.levels])
+    ab = None
+    if pyr_b is not None:
+        _cuda(coords_b, out_b, *pyr_b.levels)
+        _f32c(coords_b, "coords_b"); _rows(out_b, "out_b")
+        if ((pyr_b.n, pyr_b.h, pyr_b.w) != (n, h, w) or coords_b.shape != coords_a.shape or out_b.shape != out_a.shape
+                or out_b.stride(0) != out_a.stride(0) or out_b.dtype != torch.float16):
+            raise ValueError("corr_lookup_tiled: second set does not match the first")
+        ab = (C.c_void_p * 4)(*[l.data_ptr() for l in pyr_b.levels])
+    _lib.check(_lib.load().vfml_corr_lookup_tiled(aa, ab, n, h, w, _p(coords_a), _p(coords_b), _p(out_a), _p(out_b),
+                                                  out_a.stride(0), 0, int(math_f32), _stream()), "corr_lookup_tiled")
+    return out_a, out_b
+
+
 def convex_upsample8(flow, mask, out=None, crop=None, flow_is_coords=False):
     """flow [n, 2, h, w] fp32; mask [n, 576, h, w] fp32 or rows view [n*h*w, 576].
     crop=(top, left, out_h, out_w) selects a window of the 8h x 8w result (unpad fused);
