@@ -51,10 +51,6 @@ int vfml_version(void);
 const char* vfml_last_error(void);
 /* Number of kernels this library has launched since it was loaded (all threads). */
 uint64_t vfml_launch_count(void);
-/* Device-wide hint (cudaLimitMaxL2FetchGranularity) for the current device: 32, 64 or 128 bytes
- * fetched from DRAM per L2 sector miss.  The tiled correlation lookup gathers single 32-byte
- * sectors, so the engine asks for 32; streaming kernels are unaffected (they use whole lines). */
-int vfml_set_l2_fetch_granularity(int bytes);
 
 /* ---------------------------------------------------------------------------------
  * Layout conversion.  src [n, c, hw] fp32 planar  <->  rows [n*hw, pitch] of `dtype`.
@@ -227,6 +223,18 @@ int vfml_gemm_uses_tensor_cores(const vfml_gemm_desc* d);
 int vfml_dwconv_res_gelu(const void* x, void* y, int n_img, int h, int w, int C, int64_t pitch_x,
                          int64_t pitch_y, const float* weight, const float* bias, int k, int dtype,
                          vfml_stream_t s);
+
+/* The same operation on the tensor cores (fp16 rows in and out, fp32 accumulation; k = 7 or 15).
+ * The depthwise weights are prepacked once into a banded-Toeplitz fragment table (fp16):
+ *   packed = vfml_dwconv_packed_bytes(C, k) bytes, 16-byte aligned, written by vfml_dwconv_pack_weights
+ *   from the same fp32 tap-major [k*k, C] weight vfml_dwconv_res_gelu takes.
+ * x != y; pitches are multiples of 8 elements and >= C rounded up to 8 (the padding columns are read
+ * and written: they must belong to the row). */
+size_t vfml_dwconv_packed_bytes(int C, int k);
+int vfml_dwconv_pack_weights(const float* weight, int C, int k, void* packed, vfml_stream_t s);
+int vfml_dwconv_tc_res_gelu(const void* x, void* y, int n_img, int h, int w, int C, int64_t pitch_x,
+                            int64_t pitch_y, const void* packed, const float* bias, int k,
+                            vfml_stream_t s);
 
 /* Row softmax in place-capable form: out[r, :] = softmax(in[r, :n]) (gma.py:74). in fp32. */
 int vfml_softmax_rows(const float* in, void* out, int64_t rows, int n, int64_t ld_in, int64_t ld_out,

@@ -10,9 +10,6 @@ from video_flow_ml_b200 import ops
 from video_flow_ml_b200 import _lib
 dev = "cuda"
 torch.zeros(1, device=dev)
-if os.environ.get("L2_GRAN"):
-    _lib.check(_lib.load().vfml_set_l2_fetch_granularity(int(os.environ["L2_GRAN"])), "l2 gran")
-    print("L2 fetch granularity hint:", os.environ["L2_GRAN"])
 Fc, h, w = 3, 55, 128
 P = h * w
 Np = Fc * P

@@ -41,10 +41,11 @@ for name, M, C, Co, k in blocks:
     w1a, w1b, wpw, w2a, w2b = buf(hid, C), buf(C, hid), buf(C, C), buf(hid, C), buf(Co, hid)
     bh, bc, bo = torch.randn(hid, device=dev), torch.randn(C, device=dev), torch.randn(Co, device=dev)
     dww = torch.randn((k * k, C), device=dev) / k
+    dwp = ops.dwconv_pack_weights(dww, k)
     ops_list = [
         (f"{name}.ffn1.0 {M}x{hid}x{C} gelu", lambda: ops.gemm(x, w1a, t1, bias=bh, act="gelu"), 2.0 * M * hid * C),
         (f"{name}.ffn1.2 {M}x{C}x{hid} res gelu dw1", lambda: ops.gemm(t1, w1b, x2, bias=bc, res=x, act="gelu", dw=(bc, bc)), 2.0 * M * hid * C),
-        (f"{name}.dw{k} C={C}", lambda: ops.dwconv_res_gelu(x2, x3, M // P, h, w, dww, bc, k), 2.0 * M * C * k * k),
+        (f"{name}.dw{k} C={C} (tensor cores)", lambda: ops.dwconv_tc_res_gelu(x2, x3, M // P, h, w, dwp, bc, k), 2.0 * M * C * k * k),
         (f"{name}.pw {M}x{C}x{C} res gelu", lambda: ops.gemm(x3, wpw, x2, bias=bc, res=x3, act="gelu"), 2.0 * M * C * C),
         (f"{name}.ffn2.0 {M}x{hid}x{C} gelu", lambda: ops.gemm(x2, w2a, t1, bias=bh, act="gelu"), 2.0 * M * hid * C),
         (f"{name}.ffn2.2 {M}x{Co}x{hid}", lambda: ops.gemm(t1, w2b, out, bias=bo), 2.0 * M * hid * Co),
@@ -65,14 +66,14 @@ print(f"{'to_v^T (per frame) 128x7040x128':44s} {us:9.1f}   x{Fc}")
 total += Fc * us
 # lookup pair + glue
 f = torch.randn((Fc, 256, h, w), device=dev)
-fp = ops.corr_volume_pyramid(f, torch.randn_like(f), 4, dt)
-bp = ops.corr_volume_pyramid(f, torch.randn_like(f), 4, dt)
-us = timeit(lambda: ops.corr_volume_pyramid(f, f, 4, dt), 5)
+fp = ops.corr_volume_pyramid_tiled(f, torch.randn_like(f))
+bp = ops.corr_volume_pyramid_tiled(f, torch.randn_like(f))
+us = timeit(lambda: ops.corr_volume_pyramid_tiled(f, f), 5)
 print(f"{'corr_volume_pyramid (3 pairs)':44s} {us:9.1f} {2.0 * Fc * P * P * 256 / us / 1e6:9.1f}   (once per direction per window)")
 coords = ops.coords_grid(Fc, h, w, dev) + 4 * torch.randn((Fc, 2, h, w), device=dev)
 corr2 = buf(2 * Np, 324)
-us = timeit(lambda: ops.corr_lookup_pair(fp, bp, coords, coords, corr2[:Np], corr2[Np:]))
-print(f"{'corr_lookup_pair (same coords: L2-warm)':44s} {us:9.1f}")
+us = timeit(lambda: ops.corr_lookup_tiled(fp, bp, coords, coords, corr2[:Np], corr2[Np:]))
+print(f"{'corr_lookup_tiled (same coords: L2-warm)':44s} {us:9.1f}")
 total += us
 x400, f128, mfb = buf(Np, 400), buf(Np, 128), buf(Np, 128)
 w1, b1 = torch.randn((128, 4), device=dev), torch.randn(128, device=dev)

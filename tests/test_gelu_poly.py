@@ -1,4 +1,4 @@
-"""The polynomial GELU of the tensor-core epilogue (csrc/gemm_tc.cu gelu_poly2), re-evaluated in numpy fp32 with the
+"""The polynomial GELU of the tensor-core epilogue (csrc/gelu_poly.cuh gelu_poly2), re-evaluated in numpy fp32 with the
 coefficients parsed from the CUDA source, against the exact erf GELU: max abs error <= 3e-6 over [-12, 12]."""
 import math
 import os
@@ -6,7 +6,7 @@ import re
 
 import numpy as np
 
-SRC = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "video_flow_ml_b200", "csrc", "gemm_tc.cu")
+SRC = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "video_flow_ml_b200", "csrc", "gelu_poly.cuh")
 
 
 def test_gelu_polynomial_error():

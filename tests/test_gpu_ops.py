@@ -374,3 +374,30 @@ def test_tiled_volume_pair_launch(ops):
     ops.corr_lookup_tiled(ta, None, cu(ca), None, sa, None)
     ops.corr_lookup_tiled(tb, None, cu(cb), None, sb, None)
     assert torch.equal(oa, sa) and torch.equal(ob, sb)
+
+
+# ---------------------------------------------------------------- tensor-core depthwise convolution
+@pytest.mark.parametrize("k,C,n,h,w", [(15, 324, 2, 55, 128), (15, 128, 1, 20, 31), (7, 512, 1, 47, 39), (7, 64, 3, 70, 33), (15, 12, 1, 8, 8)])
+def test_dwconv_tc_matches_fp64(ops, k, C, n, h, w):
+    r = np.random.default_rng(k + C)
+    x = T(r.standard_normal((n * h * w, C)).astype(np.float32))
+    wt = T((r.standard_normal((k * k, C)) / k).astype(np.float32))
+    b = T(r.standard_normal(C).astype(np.float32))
+    xb, yb = rows_buf(n * h * w, C, torch.float16, pad=(-C) % 8 + 8), rows_buf(n * h * w, C, torch.float16, pad=(-C) % 8 + 8)
+    xb.copy_(x.cuda())
+    packed = ops.dwconv_pack_weights(wt.cuda(), k)
+    ops.dwconv_tc_res_gelu(xb, yb, n, h, w, packed, b.cuda(), k)
+    # reference in float64 on the fp16-rounded operands the kernel sees
+    xi = xb.cpu().double().reshape(n, h, w, C).permute(0, 3, 1, 2)
+    w64 = wt.half().double().t().reshape(C, 1, k, k)
+    conv = torch.nn.functional.conv2d(xi, w64, b.double(), padding=k // 2, groups=C)
+    want = torch.nn.functional.gelu(xi + conv).permute(0, 2, 3, 1).reshape(n * h * w, C)
+    err = (yb.cpu().double() - want).abs().max().item()
+    assert err <= 2.0 ** -10 * max(1.0, want.abs().max().item()), err      # one fp16 rounding of the result
+    # the padding columns of the rows buffer stay zero
+    base = yb._base if yb._base is not None else yb
+    assert base[:, C:].abs().max().item() == 0
+    # and it agrees with the FFMA kernel
+    y2 = rows_buf(n * h * w, C, torch.float16, pad=(-C) % 8 + 8)
+    ops.dwconv_res_gelu(xb, y2, n, h, w, wt.cuda(), b.cuda(), k)
+    assert (y2.float() - yb.float()).abs().max().item() <= 1e-2 * max(1.0, want.abs().max().item())

@@ -27,7 +27,6 @@ PROTOTYPES = {
     "vfml_version": (i32, []),
     "vfml_last_error": (C.c_char_p, []),
     "vfml_launch_count": (C.c_uint64, []),
-    "vfml_set_l2_fetch_granularity": (i32, [i32]),
     "vfml_nchw_to_rows": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp]),
     "vfml_rows_to_nchw": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp]),
     "vfml_corr_volume_workspace": (sz, [i32, i32, i32, i32, i32]),
@@ -48,6 +47,9 @@ PROTOTYPES = {
     "vfml_gemm": (i32, [C.POINTER(GemmDesc), vp]),
     "vfml_gemm_uses_tensor_cores": (i32, [C.POINTER(GemmDesc)]),
     "vfml_dwconv_res_gelu": (i32, [vp, vp, i32, i32, i32, i32, i64, i64, vp, vp, i32, i32, vp]),
+    "vfml_dwconv_packed_bytes": (sz, [i32, i32]),
+    "vfml_dwconv_pack_weights": (i32, [vp, i32, i32, vp, vp]),
+    "vfml_dwconv_tc_res_gelu": (i32, [vp, vp, i32, i32, i32, i32, i64, i64, vp, vp, i32, vp]),
     "vfml_softmax_rows": (i32, [vp, vp, i64, i32, i64, i64, i32, vp]),
     "vfml_motion_glue": (i32, [vp, vp, vp, i64, vp, i64, vp, i64, i32, vp, vp, i32, i32, i32, i32, vp]),
     "vfml_coords_add": (i32, [vp, vp, vp, i64, i32, i32, vp]),

@@ -21,12 +21,6 @@ extern "C" int vfml_version(void) { return VFML_VERSION; }
 extern "C" const char* vfml_last_error(void) { return vfml::g_err; }
 extern "C" uint64_t vfml_launch_count(void) { return vfml::g_launches.load(); }
 
-extern "C" int vfml_set_l2_fetch_granularity(int bytes) {
-    VFML_REQUIRE(bytes == 32 || bytes == 64 || bytes == 128, "set_l2_fetch_granularity: %d not in {32, 64, 128}", bytes);
-    VFML_CUDA(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)bytes));
-    return VFML_OK;
-}
-
 namespace vfml {
 bool gemm_tc_supported(const vfml_gemm_desc& d);
 int validate_gemm(const vfml_gemm_desc* d);

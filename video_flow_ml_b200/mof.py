@@ -41,7 +41,7 @@ def _pad_k(w):
 class _PCWeights:
     """PCBlock4_Deep_nopool_res parameters (stack.py:8-32) prepacked for the kernels."""
 
-    def __init__(self, sd, p, k, dev, dt, perm=None):
+    def __init__(self, sd, p, k, dev, dt, perm=None, pack=None):
         """perm (optional, LongTensor [Cin]): the block's input arrives with channel `new` holding the
         reference's channel perm[new]; every op of the block up to ffn2 is channel-wise or a 1x1
         convolution, so the permutation is folded into the weights once and costs nothing at run time."""
@@ -63,6 +63,8 @@ class _PCWeights:
         self.w2a, self.b2a = mat("ffn2.0", pin), vec("ffn2.0")
         self.w2b, self.b2b = mat("ffn2.2"), vec("ffn2.2")
         self.cin, self.hid, self.cout = C, self.w1a.shape[0], self.w2b.shape[0]
+        # tensor-core depthwise (fp16 tier): banded-Toeplitz fragment table, packed once
+        self.dwk_packed = pack(self.dwk_w, k) if pack is not None else None
 
 
 class MOFEngine:
@@ -79,12 +81,13 @@ class MOFEngine:
         e = "update_block.encoder"
         # fp16 tier: the correlation features come from the tiled lookup in its permuted channel order
         self.tiled = (dtype == torch.float16) if tiled is None else bool(tiled)
-        self.convc1 = _PCWeights(sd, e + ".convc1", 15, dev, dt, perm=self.ops.corr_lookup_perm() if self.tiled else None)
-        self.convc2 = _PCWeights(sd, e + ".convc2", 15, dev, dt)
-        self.convf2 = _PCWeights(sd, e + ".convf2", 15, dev, dt)
-        self.conv = _PCWeights(sd, e + ".conv", 15, dev, dt)
-        self.gru = _PCWeights(sd, "update_block.gru", 7, dev, dt)
-        self.fhead = _PCWeights(sd, "update_block.flow_head", 15, dev, dt)
+        pack = self.ops.dwconv_pack_weights if (dtype == torch.float16 and hasattr(self.ops, "dwconv_pack_weights")) else None
+        self.convc1 = _PCWeights(sd, e + ".convc1", 15, dev, dt, perm=self.ops.corr_lookup_perm() if self.tiled else None, pack=pack)
+        self.convc2 = _PCWeights(sd, e + ".convc2", 15, dev, dt, pack=pack)
+        self.convf2 = _PCWeights(sd, e + ".convf2", 15, dev, dt, pack=pack)
+        self.conv = _PCWeights(sd, e + ".conv", 15, dev, dt, pack=pack)
+        self.gru = _PCWeights(sd, "update_block.gru", 7, dev, dt, pack=pack)
+        self.fhead = _PCWeights(sd, "update_block.flow_head", 15, dev, dt, pack=pack)
         self.convf1_w = sd[e + ".convf1_.weight"].to(dev).float().reshape(128, 4).contiguous()
         self.convf1_b = sd[e + ".convf1_.bias"].to(dev).float().contiguous()
         self.init_mhs = sd[e + ".init_hidden_state"].to(dev).float().reshape(48).contiguous()
@@ -155,7 +158,10 @@ class MOFEngine:
         x2 = self._view(ws["sa"], M, W.cin)
         o.gemm(t1, W.w1b, x2, bias=W.b1b, res=x, act="gelu", dw=(W.dw1_w, W.dw1_b))            # gelu(x+ffn1) ; k=1 dw stage
         x3 = self._view(ws["sb"], M, W.cin)
-        o.dwconv_res_gelu(x2, x3, n_img, h, w, W.dwk_w, W.dwk_b, W.k)                          # gelu(x + dw_k(x))
+        if W.dwk_packed is not None:                                                           # gelu(x + dw_k(x))
+            o.dwconv_tc_res_gelu(x2, x3, n_img, h, w, W.dwk_packed, W.dwk_b, W.k)
+        else:
+            o.dwconv_res_gelu(x2, x3, n_img, h, w, W.dwk_w, W.dwk_b, W.k)
         x4 = self._view(ws["sa"], M, W.cin)
         o.gemm(x3, W.wpw, x4, bias=W.bpw, res=x3, act="gelu")                                  # gelu(x + pw(x))
         t2 = self._view(ws["hid"], M, W.hid)

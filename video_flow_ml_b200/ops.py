@@ -375,6 +375,36 @@ def dwconv_res_gelu(x, y, n_img, h, w, weight_tapmajor, bias, k):
     return y
 
 
+def dwconv_pack_weights(weight_tapmajor, k):
+    """fp32 tap-major [k*k, C] depthwise weight -> packed fp16 band table for dwconv_tc_res_gelu (uint8 tensor)."""
+    _cuda(weight_tapmajor)
+    _f32c(weight_tapmajor, "weight")
+    if weight_tapmajor.dim() != 2 or weight_tapmajor.shape[0] != k * k:
+        raise ValueError("dwconv_pack_weights: weight must be [k*k, C]")
+    Cc = weight_tapmajor.shape[1]
+    lib = _lib.load()
+    nbytes = lib.vfml_dwconv_packed_bytes(Cc, k)
+    if nbytes == 0:
+        raise ValueError(f"dwconv_pack_weights: unsupported k={k}")
+    packed = torch.empty(nbytes, dtype=torch.uint8, device=weight_tapmajor.device)
+    _lib.check(lib.vfml_dwconv_pack_weights(_p(weight_tapmajor), Cc, k, _p(packed), _stream()), "dwconv_pack_weights")
+    return packed
+
+
+def dwconv_tc_res_gelu(x, y, n_img, h, w, packed, bias, k):
+    """Tensor-core depthwise: y = gelu(x + dwconv_k(x) + b), fp16 rows views [n_img*h*w, C], packed from dwconv_pack_weights."""
+    _cuda(x, y, packed, bias)
+    _rows(x, "x"); _rows(y, "y")
+    Cc = x.shape[1]
+    if x.shape != y.shape or x.shape[0] != n_img * h * w or x.dtype != torch.float16 or y.dtype != torch.float16:
+        raise ValueError("dwconv_tc_res_gelu: fp16 rows views of equal shape expected")
+    if packed.numel() != _lib.load().vfml_dwconv_packed_bytes(Cc, k) or bias.numel() != Cc:
+        raise ValueError("dwconv_tc_res_gelu: packed weights / bias do not match C and k")
+    _lib.check(_lib.load().vfml_dwconv_tc_res_gelu(_p(x), _p(y), n_img, h, w, Cc, x.stride(0), y.stride(0), _p(packed),
+                                                   _p(_f32c(bias, "b")), k, _stream()), "dwconv_tc_res_gelu")
+    return y
+
+
 def softmax_rows(src, dst):
     _cuda(src, dst)
     _rows(src, "src"); _rows(dst, "dst")
