@@ -94,19 +94,19 @@ dwconv_tc_kernel(const __half* __restrict__ x, __half* __restrict__ y, int h, in
     const int n0 = tx_i * DT_TW, y0 = ty_i * DT_TH;
     const int64_t img_row0 = (int64_t)img * h * w;
 
-    // ---- 1a. band table of this channel group: K*16 uint4 per channel
+    // ---- 1a. band table of this channel group: K*16 uint4 per channel, asynchronous (lands while 1b runs)
     {
         const uint4* src = reinterpret_cast<const uint4*>(packed + (int64_t)grp * DT_CG * K * 128);
         for (int i = tid; i < DT_CG * K * 16; i += 256) {
             const int ch = i / (K * 16), o = i - ch * (K * 16);
-            const uint4 v = __ldg(src + i);
-            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(s_w + ch * WCH + o * 16), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s_w + ch * WCH + o * 16), "l"(src + i) : "memory");
         }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
     }
     // ---- 1b. transpose-load the input window: pixel-major 16-byte channel vectors -> 8 channel planes
     {
         constexpr int NPIX = INH * DT_INW;
-        constexpr int CH = 5;                              // loads in flight per thread
+        constexpr int CH = (NPIX + 255) / 256;             // every load of the thread in flight at once
         for (int p0 = 0; p0 < NPIX; p0 += 256 * CH) {
             uint4 v[CH];
 #pragma unroll
@@ -132,6 +132,7 @@ dwconv_tc_kernel(const __half* __restrict__ x, __half* __restrict__ y, int h, in
             }
         }
     }
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
     __syncthreads();
 
     // ---- 2. MMAs: warp <-> channel; 4 m-blocks (16 rows) x 4 n-blocks (8 columns)
