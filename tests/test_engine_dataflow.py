@@ -48,3 +48,19 @@ def test_engine_tiled_lookup_channel_permutation(mof_weights):
     perm = fake_ops.corr_lookup_perm()
     assert sorted(perm.tolist()) == list(range(324))
     assert perm[0] == 0 and perm[7] == 7 and perm[8] == 9 and perm[288] == 8 and perm[323] == 3 * 81 + 8 * 9 + 8
+
+
+def test_bof_engine_dataflow_matches_oracle():
+    """BOF (3-frame) variant of the engine: no hidden state, 256-channel conv block, [2->1 | 2->3] mask order."""
+    from oracle import bof as obof
+    sd = obof.bof_synthetic_weights(0)
+    frames = cases.mof_case()
+    win = omof.pad_frames(omof.frames_to_window(frames, 2, 3)).contiguous()
+    of, on, oi = obof.bof_encode(win, sd)
+    want = obof.bof_refine(of, on, oi, sd, iters=3)
+    eng = MOFEngine(sd, "cpu", torch.float32, iters=3, ops=fake_ops, arch="bof")
+    got = eng.refine(of, on, oi)
+    assert got.shape == want.shape == (1, 2, 2, 128, 192)
+    assert (got - want).abs().max() < 2e-3, (got - want).abs().max()
+    sel = eng.refine(of, on, oi, select=1)          # what VideoFlowCore returns: the 2->1 flow
+    assert (sel - want[0, 1]).abs().max() < 2e-3

@@ -148,3 +148,23 @@ def test_mof_fp16_tier_matches_reference_golden(golden):
     for idx in (2, 5):
         flow = p.compute_optical_flow(list(frames), idx)
         assert epe(flow, g[f"flow_{idx}"]) <= 5e-2, (idx, epe(flow, g[f"flow_{idx}"]))
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-2), ("fp16", 5e-2)])
+def test_bof_matches_reference_golden(golden, precision, tol):
+    """BOF architecture (3 frames, 12 iterations) against the unmodified reference BOFNet; the wrapper returns
+    the 2->1 flow (index shape[1] // 2 of the model output, processing/videoflow_core.py:192-194)."""
+    from oracle import bof as obof
+    from video_flow_ml_b200.processing import VideoFlowProcessor
+    g = golden("bof_e2e.npz")
+    p = VideoFlowProcessor("cuda", sequence_length=3, architecture="bof", dataset="things", precision=precision)
+    p.core.load_state_dict(obof.bof_synthetic_weights(0))
+    frames = cases.mof_case()
+    for idx in (2, 4):
+        flow = p.compute_optical_flow(list(frames), idx)
+        assert epe(flow, g[f"flows_{idx}"][1].transpose(1, 2, 0)) <= tol, (idx, epe(flow, g[f"flows_{idx}"][1].transpose(1, 2, 0)))
+    # all flows of the window: [2->3, 2->1]
+    win = p.prepare_frame_sequence(list(frames), 2)
+    x = torch.nn.functional.pad(win, [2, 2, 2, 2, 0, 0], mode="replicate")
+    allf = p.core.model.forward(x)[0, :, :, 2:-2, 2:-2].cpu().numpy()
+    assert np.sqrt(((allf - g["flows_2"]) ** 2).sum(1)).max() <= tol

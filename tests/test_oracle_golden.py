@@ -141,3 +141,15 @@ def test_taa(golden, name, kw):
         assert o.dtype == want.dtype, (i, o.dtype, want.dtype)
         assert np.array_equal(o, want), (name, i, np.abs(o - want).max())
         prev = flows[i].copy()
+
+
+def test_bof_oracle_matches_reference_golden(golden):
+    """oracle/bof.py against the output of the unmodified reference BOFNet (tests/golden/make_golden_bof.py)."""
+    from oracle import bof as obof
+    g = golden("bof_e2e.npz")
+    sd = obof.bof_synthetic_weights(0)
+    frames = cases.mof_case()
+    win = mof.frames_to_window(frames, 2, 3)
+    flows = mof.unpad(obof.bof_forward(mof.pad_frames(win), sd), *win.shape[-2:])[0]
+    assert np.abs(flows.numpy() - g["flows_2"]).max() < 1e-4
+    assert np.abs(obof.core_compute_flow(win, sd).numpy() - g["flows_2"][1]).max() < 1e-4

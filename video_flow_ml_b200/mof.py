@@ -71,7 +71,13 @@ class MOFEngine:
     """Stateless-per-window MOF refinement; buffers are cached per (F, h, w)."""
 
     def __init__(self, state_dict, device, dtype=torch.float32, iters=ITERS, ops=None, encoder_dtype=None, use_graph=True,
-                 tiled=None):
+                 tiled=None, arch="mof"):
+        """arch='mof': MOFNetStack (multi-frame, temporal hidden state).  arch='bof': BOFNet (3 frames, no hidden
+        state, conv block 256 -> 124, mask scale 0.25, mask channels ordered [2->1 | 2->3]),
+        BOFNet/network.py:82-145 + BOFNet/sk2.py:33-92."""
+        if arch not in ("mof", "bof"):
+            raise ValueError(f"arch must be 'mof' or 'bof', got {arch}")
+        self.arch = arch
         self.ops = ops or _ops
         self.dev = torch.device(device)
         self.dt = dtype
@@ -90,7 +96,7 @@ class MOFEngine:
         self.fhead = _PCWeights(sd, "update_block.flow_head", 15, dev, dt, pack=pack)
         self.convf1_w = sd[e + ".convf1_.weight"].to(dev).float().reshape(128, 4).contiguous()
         self.convf1_b = sd[e + ".convf1_.bias"].to(dev).float().contiguous()
-        self.init_mhs = sd[e + ".init_hidden_state"].to(dev).float().reshape(48).contiguous()
+        self.init_mhs = sd[e + ".init_hidden_state"].to(dev).float().reshape(48).contiguous() if arch == "mof" else None
         self.w_v = _pad_k(sd["update_block.aggregator.to_v.weight"].to(dev).flatten(1).to(dt))
         self.gamma = float(sd["update_block.aggregator.gamma"].reshape(-1)[0])
         self.w_qk = _pad_k(sd["att.to_qk.weight"].to(dev).flatten(1).to(dt))
@@ -99,7 +105,8 @@ class MOFEngine:
         self.w_m0 = _pad_k(m0.permute(0, 2, 3, 1).reshape(256, 9 * 128).to(dt))
         self.b_m0 = sd["update_block.mask.0.bias"].to(dev).float().contiguous()
         self.w_m2 = _pad_k(sd["update_block.mask.2.weight"].to(dev).flatten(1).to(dt))
-        self.b_m2_x100 = (100.0 * sd["update_block.mask.2.bias"].to(dev).float()).contiguous()
+        self.mask_scale = 100.0 if arch == "mof" else 0.25          # stack.py:139 / sk2.py:91
+        self.b_m2_x100 = (self.mask_scale * sd["update_block.mask.2.bias"].to(dev).float()).contiguous()
         enc_dt = encoder_dtype or torch.float32
         self.fnet = TwinsStage01(sd, "fnet.svt", dev, enc_dt) if "fnet.svt.patch_embeds.0.proj.weight" in sd else None
         self.cnet = TwinsStage01(sd, "cnet.svt", dev, enc_dt) if "cnet.svt.patch_embeds.0.proj.weight" in sd else None
@@ -121,7 +128,8 @@ class MOFEngine:
             ws = {
                 "corr2": self._rows_buf(2 * Np, 324),
                 "cor_in": self._rows_buf(Np, 256),
-                "x400": self._rows_buf(Np, 400),
+                "x400": self._rows_buf(Np, 400),      # MOF: [cor 192 | flo 64 | warped next 48 | warped prev 48 | hidden 48]
+                "x256": self._rows_buf(Np, 256) if self.arch == "bof" else None,     # BOF: [cor 192 | flo 64]
                 "f128": self._rows_buf(Np, 128),
                 "x512": self._rows_buf(Np, 512),
                 "vT": torch.zeros((Fc, 128, _pad8(h * w)), dtype=self.dt, device=self.dev),
@@ -220,12 +228,16 @@ class MOFEngine:
         self._pcblock(corr2, self.convc1, ws, 2 * Fc, h, w,
                       [(full, slice(0, Np), ws["cor_in"][:, 0:128], "gelu"),
                        (full, slice(Np, 2 * Np), ws["cor_in"][:, 128:256], "gelu")])
-        self._pcblock(ws["cor_in"], self.convc2, ws, Fc, h, w, [(full, full, x400[:, 0:192], None)])
-        self._pcblock(ws["f128"], self.convf2, ws, Fc, h, w, [(full, full, x400[:, 192:256], None)])
-        # conv: 400 -> 172 = 124 motion features + 48 new hidden state                         stack.py:97-102
-        self._pcblock(x400, self.conv, ws, Fc, h, w,
-                      [(slice(0, 124), full, x512[:, 256:380], None),
-                       (slice(124, 172), full, x400[:, 352:400], None)])
+        xin = ws["x256"] if self.arch == "bof" else x400     # BOF has no hidden state: the glue's warps land in a scratch x400
+        self._pcblock(ws["cor_in"], self.convc2, ws, Fc, h, w, [(full, full, xin[:, 0:192], None)])
+        self._pcblock(ws["f128"], self.convf2, ws, Fc, h, w, [(full, full, xin[:, 192:256], None)])
+        if self.arch == "bof":
+            self._pcblock(xin, self.conv, ws, Fc, h, w, [(full, full, x512[:, 256:380], None)])     # sk2.py:55-56
+        else:
+            # conv: 400 -> 172 = 124 motion features + 48 new hidden state                     stack.py:97-102
+            self._pcblock(x400, self.conv, ws, Fc, h, w,
+                          [(slice(0, 124), full, x512[:, 256:380], None),
+                           (slice(124, 172), full, x400[:, 352:400], None)])
         # Aggregate (gma.py:102-115): mfg = mf + gamma * attn @ to_v(mf)
         for f in range(Fc):
             rows = slice(f * P, (f + 1) * P)
@@ -249,8 +261,14 @@ class MOFEngine:
         o.gemm(col, self.w_m0, m256, bias=self.b_m0, act="relu")
         nch = chan.stop - chan.start
         mask = ws["mask"][: n_img * P, :nch]       # fp32 in both tiers: logits of the 9-tap softmax
-        o.gemm(m256, self.w_m2[chan], mask, bias=self.b_m2_x100[chan].contiguous(), alpha=100.0)
+        o.gemm(m256, self.w_m2[chan], mask, bias=self.b_m2_x100[chan].contiguous(), alpha=self.mask_scale)
         return mask
+
+    def _mask_chan(self, direction):
+        """Mask-head channels of the forward (0) / backward (1) flow: MOF [fwd | bwd] (network.py:199),
+        BOF [2->1 | 2->3] = [bwd | fwd] (BOFNet/network.py:130)."""
+        d = direction if self.arch == "mof" else 1 - direction
+        return slice(576 * d, 576 * (d + 1))
 
     def _iterations_body(self, ws, fmaps, net, inp, Fc, h, w):
         """pyramids, attention, `iters` update steps.  Leaves net in x512[:, 0:128]; returns the coords."""
@@ -260,7 +278,8 @@ class MOFEngine:
         x512 = ws["x512"]
         o.nchw_to_rows(net, x512[:, 0:128])
         o.nchw_to_rows(inp, x512[:, 128:256])
-        o.rows_fill(ws["x400"][:, 352:400], self.init_mhs)          # init_hidden_state, stack.py:72-73
+        if self.arch == "mof":
+            o.rows_fill(ws["x400"][:, 352:400], self.init_mhs)      # init_hidden_state, stack.py:72-73
         self.attention(ws, Fc, P)
         fc = o.coords_grid(Fc, h, w, self.dev)
         bc = o.coords_grid(Fc, h, w, self.dev)
@@ -306,14 +325,14 @@ class MOFEngine:
         fc, bc = self._run_iterations(ws, fmaps, net, inp, Fc, h, w)
         if select is None:
             flows = torch.empty((1, 2 * Fc, 2, 8 * h, 8 * w), dtype=torch.float32, device=self.dev)
-            mk = self.mask_rows(ws, slice(0, Fc), h, w, slice(0, 576))
+            mk = self.mask_rows(ws, slice(0, Fc), h, w, self._mask_chan(0))
             o.convex_upsample8(fc, mk, out=flows[0, :Fc], flow_is_coords=True)
-            mk = self.mask_rows(ws, slice(0, Fc), h, w, slice(576, 1152))
+            mk = self.mask_rows(ws, slice(0, Fc), h, w, self._mask_chan(1))
             o.convex_upsample8(bc, mk, out=flows[0, Fc:], flow_is_coords=True)
             return flows
         direction, frame = divmod(select, Fc)
         coords = (fc, bc)[direction][frame:frame + 1]
-        mk = self.mask_rows(ws, slice(frame, frame + 1), h, w, slice(576 * direction, 576 * (direction + 1)))
+        mk = self.mask_rows(ws, slice(frame, frame + 1), h, w, self._mask_chan(direction))
         if out is None:
             oh, ow = (crop[2], crop[3]) if crop else (8 * h, 8 * w)
             out = torch.empty((2, oh, ow), dtype=torch.float32, device=self.dev)

@@ -71,13 +71,16 @@ class VideoFlowCore:
 
     def load_state_dict(self, state_dict, model_path="<state_dict>", iters=32):
         """Build the engine from an in-memory checkpoint (upstream key names, optional 'module.' prefix)."""
-        if self.architecture != 'mof':
-            raise NotImplementedError("only the MOF architecture is implemented in this build")
+        if self.architecture not in ('mof', 'bof'):
+            raise ValueError(f"unknown architecture {self.architecture!r} (expected 'mof' or 'bof')")
         if not str(self.device).startswith("cuda"):
             raise RuntimeError("this build runs on CUDA devices only (no CPU fallback)")
         self.cfg = self._make_cfg(model_path)
+        if self.architecture == 'bof' and iters == 32:
+            iters = 12            # VideoFlow/configs/things.py:29 (BOFNet.decoder_depth)
         self.model = MOFEngine(state_dict, self.device, _PRECISIONS[self.precision], iters=iters,
-                               encoder_dtype=_PRECISIONS[self.precision] if self.precision == "fp16" else None)
+                               encoder_dtype=_PRECISIONS[self.precision] if self.precision == "fp16" else None,
+                               arch=self.architecture)
 
     # ------------------------------------------------------------------ inference
     def _validate(self, t):
