@@ -136,7 +136,7 @@ def main():
     import torch
     import torch.distributed as dist
     import cases
-    from video_flow_ml_b200 import _lib, ops
+    from video_flow_ml_b200 import _lib, ops, sharding
     from video_flow_ml_b200.processing import VideoFlowProcessor
     from oracle.mof import mof_synthetic_weights      # seeded weight generator only (a deterministic RNG)
 
@@ -156,7 +156,6 @@ def main():
     n_steps = args.steps
     windows = [proc.prepare_frame_sequence(frames, i % CLIP) for i in range(CLIP)]
     out = torch.empty((n_steps, 2, H, W), dtype=torch.float32, device=dev)
-    gathered = [torch.empty_like(out) for _ in range(world)] if (world > 1 and rank == 0) else None
 
     def barrier():
         if world > 1:
@@ -175,8 +174,8 @@ def main():
     e0.record()
     for i in range(n_steps):
         proc.core.compute_flow_from_tensor(windows[i % CLIP], out=out[i])
-    if world > 1:
-        dist.gather(out, gathered, dst=0)
+    if world > 1:      # the only communication of the job: finished flows to rank 0 (NCCL over NVLink)
+        sharding.gather_flows(out, world * n_steps, world, rank, dst=0)
     e1.record()
     barrier()
     launches = _lib.launch_count() + proc.core.model.graph_launches - n0     # direct launches + kernels replayed from the CUDA graph
