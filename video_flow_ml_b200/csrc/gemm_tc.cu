@@ -18,6 +18,7 @@
 // fp32 pairs through fma.rn.f32x2, and GELU through a degree-12 polynomial in x^2 of
 // (Phi(x) - 1/2) / x on |x| <= 5 (max abs error 2e-6, no MUFU ops).
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "gelu_poly.cuh"
@@ -43,6 +44,8 @@ struct TcParams {
     uint32_t epi;
     int out_f32;
     int vec_in_smem;
+    int b_res;           // weight-stationary mode: this CTA's B tile (all K blocks) stays in shared memory
+    long long* trace;    // debug (VFML_GEMM_TRACE=1): per-CTA cycle counters, 8 per CTA
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -129,16 +132,33 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     const int BN = p.BN, stages = p.stages;
     const uint32_t a_bytes = TC_BM * TC_BK * 2, b_bytes = (uint32_t)BN * TC_BK * 2;
     const uint32_t b_stride = (b_bytes + 1023) & ~1023u;
-    uint8_t* sA = smem;
-    uint8_t* sB = smem + (size_t)stages * a_bytes;
-    float* s_vec = reinterpret_cast<float*>(sB + (size_t)stages * b_stride);     // [3][vec_cols]: bias, dw_w, dw_b
-    __shared__ uint64_t full_bar[TC_MAX_STAGES], empty_bar[TC_MAX_STAGES], acc_full[2], acc_empty[2];
+    const int nkb = (p.K + TC_BK - 1) / TC_BK;
+    // b_res: [nkb resident B blocks][A ring]; else [A ring][B ring]
+    const int b_slots = p.b_res ? nkb : stages;
+    uint8_t* sB = p.b_res ? smem : smem + (size_t)stages * a_bytes;
+    uint8_t* sA = p.b_res ? smem + (size_t)b_slots * b_stride : smem;
+    float* s_vec = reinterpret_cast<float*>(smem + (size_t)stages * a_bytes + (size_t)b_slots * b_stride);   // [3][vec_cols]: bias, dw_w, dw_b
+    __shared__ uint64_t full_bar[TC_MAX_STAGES], empty_bar[TC_MAX_STAGES], acc_full[2], acc_empty[2], b_full;
     __shared__ uint32_t tmem_base_s;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int nkb = (p.K + TC_BK - 1) / TC_BK;
     const int tiles_per_batch = p.m_tiles * p.n_tiles;
     const int num_tiles = tiles_per_batch * p.batch;
+    // tile walk.  Default: round-robin over all (batch, m, n) tiles.  b_res (batch == 1): the CTA keeps ONE n-tile
+    // (its weights never leave shared memory) and strides over the m-tiles; gridDim.x is a multiple of n_tiles.
+    const int t_first = p.b_res ? (int)blockIdx.x / p.n_tiles : (int)blockIdx.x;
+    const int t_step = p.b_res ? (int)gridDim.x / p.n_tiles : (int)gridDim.x;
+    const int t_end = p.b_res ? p.m_tiles : num_tiles;
+    const int n_fixed = p.b_res ? ((int)blockIdx.x % p.n_tiles) * BN : 0;
+    auto tile_coords = [&](int tile, int& bz, int& m0, int& n0) {
+        if (p.b_res) {
+            bz = 0; m0 = tile * TC_BM; n0 = n_fixed;
+        } else {
+            bz = tile / tiles_per_batch;
+            const int t = tile - bz * tiles_per_batch;
+            m0 = (t / p.n_tiles) * TC_BM; n0 = (t % p.n_tiles) * BN;
+        }
+    };
     const int vec_cols = p.n_tiles * BN;
 
     if (threadIdx.x == 0) {
@@ -150,6 +170,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             mbar_init(&acc_full[b], 1);
             mbar_init(&acc_empty[b], TC_EPI_WARPS);
         }
+        mbar_init(&b_full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
@@ -174,36 +195,50 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     if (warp == 0) {
         if (lane == 0) {
             uint32_t it = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int bz = tile / tiles_per_batch, t = tile - bz * tiles_per_batch;
-                const int m0 = (t / p.n_tiles) * TC_BM, n0 = (t % p.n_tiles) * BN;
+            long long t_wait = 0, t0 = clock64();
+            if (p.b_res && t_first < t_end) {
+                mbar_expect_tx(&b_full, (uint32_t)nkb * b_bytes);
+                for (int kb = 0; kb < nkb; ++kb) tma_load_3d(&mapB, &b_full, sB + (size_t)kb * b_stride, kb * TC_BK, n_fixed, 0);
+            }
+            for (int tile = t_first; tile < t_end; tile += t_step) {
+                int bz, m0, n0;
+                tile_coords(tile, bz, m0, n0);
                 for (int kb = 0; kb < nkb; ++kb, ++it) {
                     const int s = it % stages;
                     const uint32_t ph = (it / stages) & 1u;
+                    const long long w0 = clock64();
                     mbar_wait(&empty_bar[s], ph ^ 1u);
-                    mbar_expect_tx(&full_bar[s], a_bytes + b_bytes);
+                    t_wait += clock64() - w0;
+                    mbar_expect_tx(&full_bar[s], p.b_res ? a_bytes : a_bytes + b_bytes);
                     tma_load_3d(&mapA, &full_bar[s], sA + (size_t)s * a_bytes, kb * TC_BK, m0, bz);
-                    tma_load_3d(&mapB, &full_bar[s], sB + (size_t)s * b_stride, kb * TC_BK, n0, bz);
+                    if (!p.b_res) tma_load_3d(&mapB, &full_bar[s], sB + (size_t)s * b_stride, kb * TC_BK, n0, bz);
                 }
             }
+            if (p.trace) { p.trace[blockIdx.x * 8 + 0] = t_wait; p.trace[blockIdx.x * 8 + 1] = clock64() - t0; }
         }
     } else if (warp == 1) {
         if (lane == 0) {
             // instruction descriptor: D fp32, A/B fp16, both K-major, N = BN, M = 128
             const uint32_t idesc = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
             uint32_t it = 0, tl = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
+            long long t_we = 0, t_wf = 0, t0 = clock64();
+            if (p.b_res && t_first < t_end) mbar_wait(&b_full, 0);
+            for (int tile = t_first; tile < t_end; tile += t_step, ++tl) {
                 const uint32_t buf = tl & 1u, aph = (tl >> 1) & 1u;
+                const long long w0 = clock64();
                 mbar_wait(&acc_empty[buf], aph ^ 1u);          // epilogue has drained this accumulator
+                t_we += clock64() - w0;
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t tmem_d = tmem_base + buf * 256u;
                 for (int kb = 0; kb < nkb; ++kb, ++it) {
                     const int s = it % stages;
                     const uint32_t ph = (it / stages) & 1u;
+                    const long long w1 = clock64();
                     mbar_wait(&full_bar[s], ph);
+                    t_wf += clock64() - w1;
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint64_t adesc = make_sw128_desc(smem_u32(sA + (size_t)s * a_bytes));
-                    const uint64_t bdesc = make_sw128_desc(smem_u32(sB + (size_t)s * b_stride));
+                    const uint64_t bdesc = make_sw128_desc(smem_u32(sB + (size_t)(p.b_res ? kb : s) * b_stride));
 #pragma unroll
                     for (int k = 0; k < TC_BK / 16; ++k)   // +32 bytes per K=16 step inside the 128-byte swizzle atom
                         umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) ? 1u : 0u);
@@ -211,24 +246,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 }
                 umma_commit(&acc_full[buf]);
             }
+            if (p.trace) { p.trace[blockIdx.x * 8 + 2] = t_we; p.trace[blockIdx.x * 8 + 3] = t_wf; p.trace[blockIdx.x * 8 + 4] = clock64() - t0; }
         }
     } else {
+        long long e_wait = 0, e_t0 = clock64();
         const int q = warp & 3;                   // TMEM lane quarter this warp may access
-        const int hsel = (warp - 2) >> 2;         // which half of the 16-column chunks
+        const int hsel = (warp - 2) >> 2;         // which CONTIGUOUS share of the tile's columns (contiguous: a thread's
+                                                  // consecutive 32-byte stores complete whole 128-byte lines of its row)
         const bool has_bias = p.epi & VFML_EPI_BIAS, has_res = p.epi & VFML_EPI_RES, has_dw = p.epi & VFML_EPI_DW1;
         const bool do_gelu = p.epi & VFML_EPI_GELU, do_relu = p.epi & VFML_EPI_RELU;
         const float2 alpha2 = splat(p.alpha);
         uint32_t tl = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
-            const int bz = tile / tiles_per_batch, t = tile - bz * tiles_per_batch;
-            const int m0 = (t / p.n_tiles) * TC_BM, n0 = (t % p.n_tiles) * BN;
+        for (int tile = t_first; tile < t_end; tile += t_step, ++tl) {
+            int bz, m0, n0;
+            tile_coords(tile, bz, m0, n0);
             const uint32_t buf = tl & 1u, aph = (tl >> 1) & 1u;
             const int m = m0 + q * 32 + lane;
             const bool row_ok = m < p.M;
             const __half* rrow = p.res ? p.res + bz * p.strideR + (int64_t)m * p.ldr : nullptr;
             __half* d16 = reinterpret_cast<__half*>(p.D) + bz * p.strideD + (int64_t)m * p.ldd;
             float* d32 = reinterpret_cast<float*>(p.D) + bz * p.strideD + (int64_t)m * p.ldd;
+            const long long ew0 = clock64();
             mbar_wait(&acc_full[buf], aph);
+            e_wait += clock64() - ew0;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             // software pipeline over this warp's 16-column chunks: the TMEM load and the residual load of
             // chunk i+1 are in flight while chunk i goes through the epilogue math and is stored
@@ -236,8 +276,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             const uint32_t trow = tmem_base + buf * 256u + ((uint32_t)(q * 32) << 16);
             uint32_t tc[16], tn[16];
             uint4 rc0 = make_uint4(0, 0, 0, 0), rc1 = rc0, rn0 = rc0, rn1 = rc0;
-            int c = hsel * 16;
-            if (c < BN && n0 + c < p.N) {
+            constexpr int NCS = TC_EPI_WARPS / 4;
+            const int cols_here = min(BN, p.N - n0);                       // valid columns of this tile
+            const int share = ((cols_here + 15) / 16 + NCS - 1) / NCS * 16;   // columns per warp share, multiple of 16
+            int c = hsel * share;
+            const int c_end = min(c + share, BN);
+            if (c < c_end && n0 + c < p.N) {
                 tmem_ld16_issue(trow + (uint32_t)c, tc);
                 if (res_vec && n0 + c + 16 <= p.N) {
                     rc0 = *reinterpret_cast<const uint4*>(rrow + n0 + c);
@@ -245,11 +289,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 }
                 tmem_ld_wait(tc);
             }
-            for (; c < BN; c += 32) {
+            for (; c < c_end; c += 16) {
                 const int n = n0 + c;
                 if (n >= p.N) break;                  // warp-uniform
-                const int cn = c + 32;
-                const bool has_next = cn < BN && n0 + cn < p.N;
+                const int cn = c + 16;
+                const bool has_next = cn < c_end && n0 + cn < p.N;
                 if (has_next) {
                     tmem_ld16_issue(trow + (uint32_t)cn, tn);
                     if (res_vec && n0 + cn + 16 <= p.N) {
@@ -362,6 +406,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_empty[buf]);
         }
+        if (p.trace && warp == 2 && lane == 0) { p.trace[blockIdx.x * 8 + 5] = e_wait; p.trace[blockIdx.x * 8 + 6] = clock64() - e_t0; }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -423,22 +468,6 @@ static int pick_bn(int N) {
 }
 
 int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st) {
-    const int BN = pick_bn(d.N);
-    CUtensorMap mapA, mapB;
-    int rc = make_map(&mapA, d.A, d.K, d.M, d.batch, d.lda, d.strideA, TC_BM);
-    if (rc) return rc;
-    rc = make_map(&mapB, d.B, d.K, d.N, d.batch, d.ldb, d.strideB, BN);
-    if (rc) return rc;
-    TcParams p{};
-    p.m_tiles = cdiv(d.M, TC_BM);
-    p.n_tiles = cdiv(d.N, BN);
-    const bool needs_vec = d.epi & (VFML_EPI_BIAS | VFML_EPI_DW1);
-    p.vec_in_smem = needs_vec && p.n_tiles * BN <= TC_VEC_MAX;
-    const size_t vec_bytes = p.vec_in_smem ? (size_t)3 * p.n_tiles * BN * sizeof(float) : 0;
-    const size_t a_bytes = TC_BM * TC_BK * 2, b_stride = ((size_t)BN * TC_BK * 2 + 1023) & ~(size_t)1023;
-    int stages = (int)((200 * 1024 - 1024 - vec_bytes) / (a_bytes + b_stride));
-    stages = std::max(2, std::min(stages, TC_MAX_STAGES));
-    const size_t smem = 1024 + stages * (a_bytes + b_stride) + vec_bytes;
     static int num_sms = 0;
     if (!num_sms) {
         int dev = 0;
@@ -446,14 +475,82 @@ int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st) {
         VFML_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
         VFML_CUDA(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 512));
     }
+    const size_t SMEM_MAX = 227 * 1024 - 512;
+    const size_t a_bytes = TC_BM * TC_BK * 2;
+    const int nkb = cdiv(d.K, TC_BK), m_tiles = cdiv(d.M, TC_BM);
+    const bool needs_vec = d.epi & (VFML_EPI_BIAS | VFML_EPI_DW1);
+    auto bstride = [](int bn) { return ((size_t)bn * TC_BK * 2 + 1023) & ~(size_t)1023; };
+    // (1) streaming mode: B tiles ride the ring with A
+    int BN = pick_bn(d.N);
+    int n_tiles = cdiv(d.N, BN);
+    double best_traffic = (double)n_tiles * d.M * d.K + (double)m_tiles * n_tiles * BN * d.K;      // elements through L2 -> SM
+    bool b_res = false;
+    // (2) weight-stationary mode (measured: the streaming kernel is bound by L2 -> SM operand traffic, 190 MB for a
+    // 42240 x 486 x 324 layer whose operands are 28 MB): each CTA keeps one B tile (all of K) resident and streams
+    // only A.  Pick the fewest n-tiles whose B tile fits next to >= 3 A stages, and use it when it moves fewer bytes.
+    static const bool no_res = getenv("VFML_GEMM_NO_RESIDENT") != nullptr;
+    if (d.batch == 1 && !no_res) {
+        for (int nt = 1; nt <= 16; ++nt) {
+            const int bn = ((d.N + nt - 1) / nt + 15) / 16 * 16;
+            if (bn > 256) continue;
+            const size_t vecb = needs_vec && nt * bn <= TC_VEC_MAX ? (size_t)3 * nt * bn * sizeof(float) : 0;
+            if (1024 + nkb * bstride(bn) + 3 * a_bytes + vecb > SMEM_MAX) continue;
+            const int grid_r = std::max(1, num_sms / nt) * nt;
+            const double traffic = (double)nt * d.M * d.K + (double)grid_r * bn * d.K;
+            if (m_tiles * nt >= num_sms && traffic < 0.8 * best_traffic) {
+                b_res = true; BN = bn; n_tiles = nt; best_traffic = traffic;
+            }
+            break;
+        }
+    }
+    CUtensorMap mapA, mapB;
+    int rc = make_map(&mapA, d.A, d.K, d.M, d.batch, d.lda, d.strideA, TC_BM);
+    if (rc) return rc;
+    rc = make_map(&mapB, d.B, d.K, d.N, d.batch, d.ldb, d.strideB, BN);
+    if (rc) return rc;
+    TcParams p{};
+    p.m_tiles = m_tiles;
+    p.n_tiles = n_tiles;
+    p.b_res = b_res;
+    p.vec_in_smem = needs_vec && p.n_tiles * BN <= TC_VEC_MAX;
+    const size_t vec_bytes = p.vec_in_smem ? (size_t)3 * p.n_tiles * BN * sizeof(float) : 0;
+    const size_t b_stride = bstride(BN);
+    int stages;
+    size_t smem;
+    if (b_res) {
+        stages = (int)((SMEM_MAX - 1024 - vec_bytes - nkb * b_stride) / a_bytes);
+        stages = std::max(2, std::min(stages, TC_MAX_STAGES));
+        smem = 1024 + nkb * b_stride + stages * a_bytes + vec_bytes;
+    } else {
+        stages = (int)((200 * 1024 - 1024 - vec_bytes) / (a_bytes + b_stride));
+        stages = std::max(2, std::min(stages, TC_MAX_STAGES));
+        smem = 1024 + stages * (a_bytes + b_stride) + vec_bytes;
+    }
     p.D = d.D; p.bias = d.bias; p.res = reinterpret_cast<const __half*>(d.res); p.dw_w = d.dw_w; p.dw_b = d.dw_b;
     p.ldd = d.ldd; p.ldr = d.ldr; p.strideD = d.strideD; p.strideR = d.strideR;
     p.M = d.M; p.N = d.N; p.K = d.K; p.batch = d.batch; p.BN = BN; p.stages = stages;
     p.alpha = d.alpha; p.epi = d.epi; p.out_f32 = d.out_dtype == VFML_F32;
     const int64_t num_tiles = (int64_t)p.m_tiles * p.n_tiles * d.batch;
-    const int grid = (int)std::min<int64_t>(num_tiles, num_sms);
+    const int grid = b_res ? std::max(1, num_sms / n_tiles) * n_tiles : (int)std::min<int64_t>(num_tiles, num_sms);
+    static const bool trace = getenv("VFML_GEMM_TRACE") != nullptr;
+    static long long* trace_buf = nullptr;
+    if (trace) {
+        if (!trace_buf) VFML_CUDA(cudaMalloc(&trace_buf, 148 * 8 * sizeof(long long)));
+        VFML_CUDA(cudaMemsetAsync(trace_buf, 0, 148 * 8 * sizeof(long long), st));
+        p.trace = trace_buf;
+    }
     gemm_tc_kernel<<<grid, TC_THREADS, smem, st>>>(mapA, mapB, p);
     VFML_LAUNCH_CHECK("gemm_tc");
+    if (trace) {      // debug only: synchronises
+        long long h[148 * 8];
+        VFML_CUDA(cudaMemcpyAsync(h, trace_buf, sizeof(h), cudaMemcpyDeviceToHost, st));
+        VFML_CUDA(cudaStreamSynchronize(st));
+        double a[8] = {0};
+        for (int c = 0; c < grid; ++c)
+            for (int i = 0; i < 8; ++i) a[i] += (double)h[c * 8 + i] / grid;
+        fprintf(stderr, "[gemm_tc trace] M=%d N=%d K=%d BN=%d stages=%d tiles=%lld epi=%u res=%d | producer wait_empty %.0f of %.0f | mma wait_acc_empty %.0f wait_full %.0f of %.0f | epilogue(warp2) wait_acc_full %.0f of %.0f cycles (avg per CTA)\n",
+                d.M, d.N, d.K, BN, stages, (long long)num_tiles, d.epi, (int)b_res, a[0], a[1], a[2], a[3], a[4], a[5], a[6]);
+    }
     return VFML_OK;
 }
 
