@@ -233,6 +233,8 @@ def main():
     torch.cuda.synchronize()
     lk_ms = l0.elapsed_time(l1) / reps          # one launch = forward + backward lookup of one iteration
     es = 4 if eng.dt == torch.float32 else 2
+    # DRAM bytes per launch of the roofline kernel on this workload, from the committed ncu --set full capture
+    NCU_TRAFFIC = {"corr_lookup_tiled_kernel": 74434048 + 4427776}
     alg_bytes = 2 * Fc * P * (4 * 100 * es + 8 + 324 * es)   # per pixel-direction 100 texels/level read + coords + 324 written
     peak, peak_kind = peaks()
     achieved = alg_bytes / (lk_ms * 1e-3) / 1e9
@@ -253,13 +255,15 @@ def main():
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32" if args.precision == "fp32" else "f16", "data": "synthetic",
         "config": {"workload": WORKLOAD, "iterations": args.iters, "precision": args.precision,
-                   "l2": "inputs larger than L2 (1.58 GB of correlation volumes per window)",
+                   "l2": "inputs larger than L2 (%s of correlation volumes per window)" % ("1.58 GB" if args.precision == "fp32" else "811 MB"),
                    "sharding": f"{world} rank(s), windows sharded, flows gathered to rank 0 (NCCL) inside the timed region"},
         "clocks": clocks,
         "e2e": {"value": total / (e2e_ms_max / 1000.0), "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": int(launches),
         "roofline": {"kernel": lk_kernel, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_kind,
+                     "frac": achieved / peak, "traffic": NCU_TRAFFIC.get(lk_kernel), "peak_source": peak_kind,
+                     "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full capture of this command "
+                                       "(profiles/r1_lookup_tiled_ncu_summary.txt; cold L2)" if lk_kernel in NCU_TRAFFIC else None,
                      "algorithmic_bytes_per_launch": alg_bytes, "us_per_launch": lk_ms * 1000.0},
     }
     if not args.no_cpu_baseline and world == 1:

@@ -16,7 +16,7 @@ import torch.nn.functional as F
 
 from . import mof as omof
 
-ITERS = 12      # VideoFlow/configs/things.py:29 (BOFNet.decoder_depth)
+ITERS = 12      # VideoFlow/configs/things.py:31 (BOFNet.decoder_depth)
 
 
 def bof_param_shapes():

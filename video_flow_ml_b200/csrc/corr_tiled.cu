@@ -8,14 +8,20 @@
 //   stored x-major: element (xr, yy) = texel (4*tx + xr, 4*ty + yy); texels beyond the level are zero.
 //
 // The 10x10 footprint of the 81 taps then touches (10+3)/4 = 3.25 tiles per axis = 10.6 sectors
-// per level on average, against 15.6 sectors for ten 20-byte row segments of the row-major slab;
-// every load is one aligned 16-byte cp.async (zero-filled outside the slab: the reference's zeros
-// padding) straight into shared memory, no registers held while it is in flight.
+// per level on average, against 15.6 sectors for ten 20-byte row segments of the row-major slab,
+// and the 4 tiles of a tile column are one contiguous 128-byte line.  Measured on B200
+// (scripts/micro/sector_gather.cu): random gathers are served at ~30 G requests/s whatever the
+// request size up to a line, and cp.async.cg / zero-fill lanes cost full requests, so the loads
+// are predicated register loads (ld.global.nc.L1::no_allocate.v4, zeros outside the slab: the
+// reference's zeros padding) issued two rounds ahead of their use.
 //
 // Lookup kernel: a warp owns a contiguous range of pixels and walks it in rounds of 3 pixels x 1
-// level through a 6-deep cp.async ring (5 rounds = 15 footprints in flight per warp, 16 warps per
-// SM).  In a round, lane = (pixel v, x-column i in 0..9): it reads its x-column (the y run is
-// contiguous in the x-major tile), interpolates along y, takes column i+1 from the next lane by
+// level.  12 header lanes (pixel, level) turn the next batch's coordinates into tile origin,
+// sub-tile offset, fractional weights and a 16-bit tile mask in shared memory; every lane then
+// loads its half tile of the 4 x 4 tile footprint for each of the 3 pixels into registers, and
+// one round later stores them to a ping-pong smem stage.  In the compute phase lane = (pixel v,
+// x-column i in 0..9): it reads its x-column (the y run is contiguous in the x-major tile,
+// realigned with a funnel shift), interpolates along y, takes column i+1 from the next lane by
 // shuffle and interpolates along x.  Its 9 results are taps (i, j=0..8) of the reference's channel
 // order l*81 + i*9 + j; they are written as ONE 16-byte store + one 2-byte store using the channel
 // order   c' = (l*9 + i)*8 + j  (j < 8),   c' = 288 + l*9 + i  (j = 8),

@@ -77,7 +77,7 @@ class VideoFlowCore:
             raise RuntimeError("this build runs on CUDA devices only (no CPU fallback)")
         self.cfg = self._make_cfg(model_path)
         if self.architecture == 'bof' and iters == 32:
-            iters = 12            # VideoFlow/configs/things.py:29 (BOFNet.decoder_depth)
+            iters = 12            # VideoFlow/configs/things.py:31 (BOFNet.decoder_depth)
         self.model = MOFEngine(state_dict, self.device, _PRECISIONS[self.precision], iters=iters,
                                encoder_dtype=_PRECISIONS[self.precision] if self.precision == "fp16" else None,
                                arch=self.architecture)
