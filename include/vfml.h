@@ -99,6 +99,20 @@ int vfml_corr_lookup_pair(const void* const* levels_fwd, const void* const* leve
                           int out_col, int out_dtype, vfml_stream_t s);
 
 /* ---------------------------------------------------------------------------------
+ * Volume-free lookup.  Replaces alt_cuda_corr.forward -- the reference's one native FFI on this path
+ * (VideoFlow/alt_cuda_corr/correlation.cpp:23-33,51-54; kernel correlation_kernel.cu:18-119), called per
+ * pyramid level by AlternateCorrBlock.__call__ (MOFNetStack/corr.py:160-177).
+ *   fmap1  : [B, H1, W1, C] NHWC, fmap_dtype      fmap2 : [B, H2, W2, C] NHWC, fmap_dtype
+ *   coords : [B, N, H1, W1, 2] fp32 (x, y) in fmap2 pixels
+ *   corr   : [B, N, (2r+1)^2, H1, W1] fp32; channel ix*(2r+1) + iy = bilinear sample (zeros outside) of
+ *            <fmap1[b,h1,w1,:], fmap2[b,.,.,:]> at (x - r + ix, y - r + iy).  No 1/sqrt(C) factor, like the
+ *            reference (the Python caller divides).  Fully overwritten (the reference accumulates into zeros).
+ *   C must be 128, 256 or 512 (fp16 also 1024); radius 1..4.
+ * ------------------------------------------------------------------------------- */
+int vfml_alt_corr_forward(const void* fmap1, const void* fmap2, const float* coords, float* corr, int B, int N,
+                          int H1, int W1, int H2, int W2, int C, int radius, int fmap_dtype, vfml_stream_t s);
+
+/* ---------------------------------------------------------------------------------
  * Gather-friendly ("tiled") fp16 pyramid + lookup: the engine's layout of the same data.
  * Replaces the same reference code as vfml_corr_volume_pyramid / vfml_corr_lookup
  * (MOFNetStack/corr.py:59-97, core/utils/utils.py:62-76).

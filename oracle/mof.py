@@ -102,6 +102,53 @@ def corr_lookup(pyr, coords, radius=CORR_RADIUS):
     return torch.cat(out, -1).permute(0, 3, 1, 2).contiguous().float()
 
 
+def alt_corr_forward(fmap1, fmap2, coords, r):
+    """alt_cuda_corr.forward restated (VideoFlow/alt_cuda_corr/correlation_kernel.cu:18-119): fmap1 [B,H1,W1,C],
+    fmap2 [B,H2,W2,C] NHWC, coords [B,N,H1,W1,2] (x, y) -> corr [B,N,(2r+1)^2,H1,W1].  For every query the kernel
+    forms s[iy][ix] = <f1, f2[floor(y)-r+iy, floor(x)-r+ix]> (0 out of bounds, :66-87) on the (2r+2)^2 integer grid
+    and scatters it with the weights nw = dy*dx, ne = dy*(1-dx), sw = (1-dy)*dx, se = (1-dy)*(1-dx) into channel
+    iy' + (2r+1)*ix' (:89-112), i.e. an x-major tap order and no 1/sqrt(C) factor.
+    PARITY UNPINNED directly (the extension needs a GPU build to run); anchored on its documented equivalence with
+    CorrBlock (VideoFlow/README.md:112, corr.py:149-177 vs :59-97), which tests/test_oracle_golden.py checks."""
+    B, H1, W1, C = fmap1.shape
+    H2, W2 = fmap2.shape[1:3]
+    N = coords.shape[1]
+    rd = 2 * r + 1
+    x, y = coords[..., 0].double(), coords[..., 1].double()              # [B,N,H1,W1]
+    fx, fy = torch.floor(x), torch.floor(y)
+    dx, dy = (x - fx), (y - fy)
+    f1 = fmap1.double()
+    f2 = fmap2.double().reshape(B, H2 * W2, C)
+    s = torch.zeros(B, N, rd + 1, rd + 1, H1, W1, dtype=torch.float64)
+    for iy in range(rd + 1):
+        for ix in range(rd + 1):
+            h2 = (fy - r + iy).long()
+            w2 = (fx - r + ix).long()
+            ok = (h2 >= 0) & (h2 < H2) & (w2 >= 0) & (w2 < W2)
+            idx = (h2.clamp(0, H2 - 1) * W2 + w2.clamp(0, W2 - 1)).reshape(B, N * H1 * W1)
+            g = torch.gather(f2, 1, idx.unsqueeze(-1).expand(-1, -1, C)).reshape(B, N, H1, W1, C)
+            s[:, :, iy, ix] = (g * f1.unsqueeze(1)).sum(-1) * ok
+    out = torch.zeros(B, N, rd * rd, H1, W1, dtype=torch.float64)
+    for ix in range(rd):
+        for iy in range(rd):
+            out[:, :, iy + rd * ix] = ((1 - dy) * (1 - dx) * s[:, :, iy, ix] + (1 - dy) * dx * s[:, :, iy, ix + 1]
+                                       + dy * (1 - dx) * s[:, :, iy + 1, ix] + dy * dx * s[:, :, iy + 1, ix + 1])
+    return out.float()
+
+
+def alt_corr_block(fmap1, fmap2, coords, num_levels=CORR_LEVELS, radius=CORR_RADIUS):
+    """AlternateCorrBlock(fmap1, fmap2)(coords), MOFNetStack/corr.py:149-177: fmap [B,C,h,w], coords [B,2,h,w]."""
+    c = coords.permute(0, 2, 3, 1)
+    B, H, W, _ = c.shape
+    f1 = fmap1.permute(0, 2, 3, 1).contiguous()
+    out = []
+    for i in range(num_levels):
+        f2 = fmap2.permute(0, 2, 3, 1).contiguous()
+        out.append(alt_corr_forward(f1, f2, (c / 2 ** i).reshape(B, 1, H, W, 2), radius).squeeze(1))
+        fmap2 = F.avg_pool2d(fmap2, 2, stride=2)
+    return torch.stack(out, 1).reshape(B, -1, H, W) / torch.sqrt(torch.tensor(fmap1.shape[1]).float())
+
+
 # ----------------------------------------------------------------------------
 # update block                         MOF/stack.py, MOF/gma.py
 # ----------------------------------------------------------------------------

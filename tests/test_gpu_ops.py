@@ -401,3 +401,48 @@ def test_dwconv_tc_matches_fp64(ops, k, C, n, h, w):
     y2 = rows_buf(n * h * w, C, torch.float16, pad=(-C) % 8 + 8)
     ops.dwconv_res_gelu(xb, y2, n, h, w, wt.cuda(), b.cuda(), k)
     assert (y2.float() - yb.float()).abs().max().item() <= 1e-2 * max(1.0, want.abs().max().item())
+
+
+# ---------------------------------------------------------------- volume-free lookup (alt_cuda_corr)
+@pytest.mark.parametrize("dt,tol", [(torch.float32, 2e-4), (torch.float16, 2e-2)])
+@pytest.mark.parametrize("B,N,H1,W1,H2,W2,C,r", [(2, 1, 16, 24, 16, 24, 256, 4), (1, 2, 9, 7, 5, 11, 128, 3),
+                                                  (1, 1, 13, 5, 13, 5, 512, 4), (3, 1, 6, 6, 3, 3, 256, 1)])
+def test_alt_corr_forward_matches_oracle(ops, dt, tol, B, N, H1, W1, H2, W2, C, r):
+    g = np.random.default_rng(B * 1000 + C + r)
+    f1 = T(g.standard_normal((B, H1, W1, C)).astype(np.float32)).to(dt)
+    f2 = T(g.standard_normal((B, H2, W2, C)).astype(np.float32)).to(dt)
+    coords = T((g.uniform(-6, 6, (B, N, H1, W1, 2)) + np.array([W2, H2]) * g.uniform(0, 1, (B, N, H1, W1, 2))).astype(np.float32))
+    coords[0, 0, 0, 0] = torch.tensor([2.0, 3.0])               # exact integers: dx = dy = 0
+    coords[0, 0, 0, 1] = torch.tensor([-1.0e9, 4.0])
+    coords[0, 0, 0, 2] = torch.tensor([W2 - 1.0, H2 - 1.0])
+    want = omof.alt_corr_forward(f1.float(), f2.float(), coords, r)
+    got, = ops.alt_corr_forward(cu(f1), cu(f2), cu(coords), r)
+    assert got.shape == (B, N, (2 * r + 1) ** 2, H1, W1) and got.dtype == torch.float32
+    close(got, want, tol * float(C) ** 0.5)
+    nanc = coords.clone()
+    nanc[0, 0, 0, 3, 0] = float("nan")                          # UB in the reference; here: zeros, nothing else disturbed
+    got2, = ops.alt_corr_forward(cu(f1), cu(f2), cu(nanc), r)
+    assert torch.all(got2[0, 0, :, 0, 3] == 0) and torch.isfinite(got2).all()
+    got2[0, 0, :, 0, 3] = got[0, 0, :, 0, 3]
+    assert torch.equal(got2, got)
+
+
+def test_alternate_corrblock_dropin(ops, golden):
+    from video_flow_ml_b200.corr import AlternateCorrBlock
+    g = golden("corr_lookup.npz")
+    f1, f2, coords = cases.lookup_case()
+    blk = AlternateCorrBlock(cu(f1), cu(f2), num_levels=4, radius=4)
+    out = blk(cu(coords))
+    assert out.shape == (2, 324, 16, 24) and out.dtype == torch.float32
+    close(out, T(g["lookup"]), 5e-5)
+
+
+def test_alt_corr_errors(ops):
+    f = torch.zeros((1, 4, 4, 96), device="cuda")
+    c = torch.zeros((1, 1, 4, 4, 2), device="cuda")
+    with pytest.raises(RuntimeError, match="unsupported"):
+        ops.alt_corr_forward(f, f, c, 4)
+    with pytest.raises(ValueError):
+        ops.alt_corr_forward(f.permute(0, 2, 1, 3), f, c, 4)
+    with pytest.raises(RuntimeError, match="radius"):
+        ops.alt_corr_forward(torch.zeros((1, 4, 4, 128), device="cuda"), torch.zeros((1, 4, 4, 128), device="cuda"), c, 5)

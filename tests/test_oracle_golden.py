@@ -153,3 +153,33 @@ def test_bof_oracle_matches_reference_golden(golden):
     flows = mof.unpad(obof.bof_forward(mof.pad_frames(win), sd), *win.shape[-2:])[0]
     assert np.abs(flows.numpy() - g["flows_2"]).max() < 1e-4
     assert np.abs(obof.core_compute_flow(win, sd).numpy() - g["flows_2"][1]).max() < 1e-4
+
+
+def test_alt_corr_oracle_matches_reference_corrblock(golden):
+    """The volume-free restatement (alt_cuda_corr + AlternateCorrBlock) against the reference CorrBlock output:
+    the two reference blocks are documented as interchangeable (VideoFlow/README.md:112)."""
+    g = golden("corr_lookup.npz")
+    f1, f2, coords = cases.lookup_case()
+    out = mof.alt_corr_block(T(f1), T(f2), T(coords))
+    assert out.shape == (2, 324, 16, 24)
+    close(out.numpy(), g["lookup"], 3e-5)
+
+
+def test_memflow_oracle_matches_reference_golden(golden):
+    """oracle/memflow.py against the reference MemFlowNet + InferenceCore (make_golden_memflow.py): a 3-step
+    sequence (memory empty / one stored frame / replaced) and the application's fresh-core end=True call."""
+    from oracle import memflow as omem
+    g = golden("memflow_e2e.npz")
+    sd = omem.memflow_synthetic_weights(0)
+    frames = cases.mof_case()
+    x = torch.stack([T(f).permute(2, 0, 1) for f in frames[:4]])[None]
+    x = mof.pad_frames(2 * (x / 255.0) - 1.0)
+    core = omem.InferenceCore(sd)
+    for t in range(2):           # step 2 is covered on the GPU (CPU time)
+        low, up = core.step(x[:, t:t + 2])
+        close(low.numpy(), g[f"seq_low_{t}"], 2e-5)
+        close(up.numpy(), g[f"seq_up_{t}"], 2e-4)
+    assert core.mem_k.shape == (1, 128, 16 * 24) and core.mem_v.shape == (1, 128, 16 * 24)
+    flow = omem.core_compute_flow(mof.frames_to_window(frames, 2, 3), sd)
+    assert flow.shape == (2, 124, 188)
+    close(flow.numpy(), g["core_flow"], 2e-4)

@@ -33,6 +33,7 @@ PROTOTYPES = {
     "vfml_corr_volume_pyramid": (i32, [vp, vp, i32, i32, i32, i32, C.POINTER(vp), i32, i32, vp, sz, vp]),
     "vfml_corr_lookup": (i32, [C.POINTER(vp), i32, i32, i32, i32, i32, i32, vp, vp, i32, i32, i32, i32, vp]),
     "vfml_corr_lookup_pair": (i32, [C.POINTER(vp), C.POINTER(vp), i32, i32, i32, i32, i32, vp, vp, vp, vp, i32, i32, i32, vp]),
+    "vfml_alt_corr_forward": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
     "vfml_corr_tiled_slab_bytes": (sz, [i32, i32, i32]),
     "vfml_corr_tile_pyramid": (i32, [vp, i64, i32, i32, C.POINTER(vp), i32, vp]),
     "vfml_corr_volume_tiled_workspace": (sz, [i32, i32, i32, i32]),

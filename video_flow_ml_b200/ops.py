@@ -123,6 +123,26 @@ def corr_lookup(levels, coords, radius=4, out=None, out_dtype=torch.float32):
     return out
 
 
+def alt_corr_forward(fmap1, fmap2, coords, radius):
+    """alt_cuda_corr.forward (correlation.cpp:23-33): fmap1 [B,H1,W1,C], fmap2 [B,H2,W2,C] NHWC contiguous (fp32 or fp16),
+    coords [B,N,H1,W1,2] fp32 -> [corr [B,N,(2r+1)^2,H1,W1] fp32] (a one-element list, like the reference binding)."""
+    _cuda(fmap1, fmap2, coords)
+    _f32c(coords, "coords")
+    if fmap1.dim() != 4 or fmap2.dim() != 4 or coords.dim() != 5 or coords.shape[-1] != 2:
+        raise ValueError("alt_corr_forward: expected fmap [B,H,W,C] and coords [B,N,H1,W1,2]")
+    for t, name in ((fmap1, "fmap1"), (fmap2, "fmap2")):
+        if not t.is_contiguous():                      # CHECK_CONTIGUOUS, correlation.cpp:19-21
+            raise ValueError(f"alt_corr_forward: {name} must be contiguous")
+    B, H1, W1, Cc = fmap1.shape
+    if fmap2.shape[0] != B or fmap2.shape[3] != Cc or fmap2.dtype != fmap1.dtype or tuple(coords.shape[2:4]) != (H1, W1) or coords.shape[0] != B:
+        raise ValueError("alt_corr_forward: shape mismatch")
+    N = coords.shape[1]
+    corr = torch.empty((B, N, (2 * radius + 1) ** 2, H1, W1), dtype=torch.float32, device=fmap1.device)
+    _lib.check(_lib.load().vfml_alt_corr_forward(_p(fmap1), _p(fmap2), _p(coords), _p(corr), B, N, H1, W1, fmap2.shape[1],
+                                                 fmap2.shape[2], Cc, radius, _dt(fmap1), _stream()), "alt_corr_forward")
+    return [corr]
+
+
 def corr_lookup_pair(levels_f, levels_b, coords_f, coords_b, out_f, out_b):
     """Forward + backward radius-4 lookups in one launch; out_f / out_b: rows views [n*h*w, 324] of equal pitch."""
     _cuda(coords_f, coords_b, out_f, out_b, *levels_f, *levels_b)
