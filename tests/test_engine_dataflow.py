@@ -1,6 +1,7 @@
 """Host-side orchestration of the MOF engine (buffer carving, column ranges, call order, weight
 prepacking) against the oracle, with the libvfml ops replaced by the CPU test double."""
 import numpy as np
+import pytest
 import torch
 
 import cases
@@ -64,3 +65,34 @@ def test_bof_engine_dataflow_matches_oracle():
     assert (got - want).abs().max() < 2e-3, (got - want).abs().max()
     sel = eng.refine(of, on, oi, select=1)          # what VideoFlowCore returns: the 2->1 flow
     assert (sel - want[0, 1]).abs().max() < 2e-3
+
+
+def test_memflow_engine_dataflow_matches_oracle():
+    """MemFlow engine (memory slots, once-per-frame affinity, 4-column glue trick) on CPU doubles vs the oracle's
+    InferenceCore: three steps so the memory is empty, then engaged, then replaced; plus end=True and flow_init."""
+    from oracle import memflow as omem
+    from video_flow_ml_b200.memflow import MemFlowEngine
+    sd = omem.memflow_synthetic_weights(0)
+    frames = cases.mof_case()
+    x = torch.stack([torch.from_numpy(f).permute(2, 0, 1) for f in frames[:4]])[None]
+    x = omof.pad_frames(2 * (x / 255.0) - 1.0).contiguous()
+    want_core = omem.InferenceCore(sd, iters=3)
+    for tiled in (False, True):
+        eng = MemFlowEngine(sd, "cpu", torch.float32, config={"val_decoder_depth": 3}, ops=fake_ops, tiled=tiled)
+        want_core.clear_memory()
+        for t in range(3):
+            wl, wu = want_core.step(x[:, t:t + 2])
+            gl, gu = eng.step(x[:, t:t + 2])
+            assert gl.shape == wl.shape == (1, 2, 16, 24) and gu.shape == wu.shape == (1, 2, 128, 192)
+            assert (gl - wl).abs().max() < 2e-4 and (gu - wu).abs().max() < 2e-3, (t, (gu - wu).abs().max())
+            assert eng.n_stored == 1
+    # end=True never memorises; flow_init shifts the starting coordinates (MemFlow.py:95-96)
+    eng.clear_memory()
+    want_core.clear_memory()
+    fi = 0.5 * torch.ones(1, 2, 16, 24)
+    wl, wu = want_core.step(x[:, 1:3], end=True, flow_init=fi)
+    gl, gu = eng.step(x[:, 1:3], end=True, flow_init=fi)
+    assert eng.n_stored == 0 and want_core.mem_k is None
+    assert (gu - wu).abs().max() < 2e-3
+    with pytest.raises(ValueError):
+        eng.step(x[:, 0:3])

@@ -168,3 +168,48 @@ def test_bof_matches_reference_golden(golden, precision, tol):
     x = torch.nn.functional.pad(win, [2, 2, 2, 2, 0, 0], mode="replicate")
     allf = p.core.model.forward(x)[0, :, :, 2:-2, 2:-2].cpu().numpy()
     assert np.sqrt(((allf - g["flows_2"]) ** 2).sum(1)).max() <= tol
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-2), ("fp16", 5e-2)])
+def test_memflow_matches_reference_golden(golden, precision, tol):
+    """MemFlow (15 iterations) against the unmodified reference MemFlowNet + InferenceCore: a 3-step sequence through
+    the stateful InferenceCore mirror (memory empty / one stored frame / replaced), then the application's call
+    (MemFlowCore.compute_flow_from_tensor: fresh memory, last two frames, end=True, unpad)."""
+    from oracle import memflow as omem
+    from video_flow_ml_b200.processing import InferenceCore, MemFlowCore, MemFlowProcessor
+    g = golden("memflow_e2e.npz")
+    core = MemFlowCore("cuda", precision=precision)
+    with pytest.raises(RuntimeError):
+        core.compute_flow_from_tensor(torch.zeros(1, 2, 3, 64, 64))
+    with pytest.raises(FileNotFoundError):
+        core.load_model()
+    core.load_state_dict({"module." + k: v for k, v in omem.memflow_synthetic_weights(0).items()})
+    frames = cases.mof_case()
+    x = torch.stack([torch.from_numpy(f).permute(2, 0, 1) for f in frames[:4]])[None]
+    x = omof.pad_frames(2 * (x / 255.0) - 1.0).contiguous().cuda()
+    ic = InferenceCore(core.model)
+    for rep in range(2):                    # second pass: cleared memory, replayed graphs
+        ic.clear_memory()
+        for t in range(3):
+            low, up = ic.step(x[:, t:t + 2])
+            e_low = epe(low[0].permute(1, 2, 0).cpu().numpy(), g[f"seq_low_{t}"][0].transpose(1, 2, 0))
+            e_up = epe(up[0].permute(1, 2, 0).cpu().numpy(), g[f"seq_up_{t}"][0].transpose(1, 2, 0))
+            assert e_up <= tol and e_low <= tol / 8 + 1e-3, (rep, t, e_low, e_up)
+            assert core.model.n_stored == 1
+    win = omof.frames_to_window(frames, 2, 3)
+    flow = core.compute_flow_from_tensor(win)
+    assert flow.shape == (2, 124, 188) and flow.device.type == "cpu"
+    assert epe(flow.permute(1, 2, 0).numpy(), g["core_flow"].transpose(1, 2, 0)) <= tol
+    for bad, exc in ((torch.zeros(1, 1, 3, 64, 64), ValueError), (torch.zeros(2, 2, 3, 64, 64), ValueError),
+                     (torch.zeros(1, 2, 3, 32, 64), ValueError), (np.zeros((1, 2, 3, 64, 64)), TypeError)):
+        with pytest.raises(exc):
+            core.compute_flow_from_tensor(bad)
+    # processor plumbing: uint8 frames, numpy [H, W, 2] out, same value as the core on the same window
+    p = MemFlowProcessor("cuda", precision=precision)
+    p.core_engine = core
+    u8 = [np.clip(f, 0, 255).astype(np.uint8) for f in frames]
+    out = p.compute_optical_flow(u8, 3)
+    assert out.shape == (124, 188, 2) and out.dtype == np.float32
+    want = core.compute_flow_from_tensor(p.prepare_frame_sequence(u8, 3)).permute(1, 2, 0).numpy()
+    assert np.array_equal(out, want)
+    assert p.calculate_tile_grid(188, 124)[2:4] == (1, 1)
