@@ -46,6 +46,17 @@ class BasicEncoder:
     @torch.no_grad()
     def __call__(self, x):
         """[N, 3, H, W] -> [N, 256, H/8, W/8] fp32"""
+        if self.dt != torch.float32 or not x.is_cuda:
+            return self._forward(x)
+        # fp32 tier: true fp32 library math (cuDNN defaults to TF32 for convolutions)
+        c = torch.backends.cudnn.allow_tf32
+        torch.backends.cudnn.allow_tf32 = False
+        try:
+            return self._forward(x)
+        finally:
+            torch.backends.cudnn.allow_tf32 = c
+
+    def _forward(self, x):
         x = F.relu(self._norm(self._conv(x.to(self.dt), "conv1", stride=2, padding=3), "norm1"))
         for li, stride in ((1, 1), (2, 2), (3, 2)):
             x = self._block(x, f"layer{li}.0", stride)

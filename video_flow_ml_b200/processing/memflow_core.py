@@ -75,8 +75,9 @@ class MemFlowCore:
     def load_state_dict(self, state_dict, config=None):
         """Build the engine from an in-memory checkpoint (upstream key names, optional 'module.' prefix)."""
         dt = _PRECISIONS[self.precision]
-        self.model = MemFlowEngine(state_dict, self.device, dt, config=config,
-                                   encoder_dtype=dt if self.precision == "fp16" else None)
+        # encoders stay fp32 in both tiers: the reference's InferenceCore.step runs outside autocast
+        # (inference_core_skflow.py:20-54), only its flash read-out is reduced precision
+        self.model = MemFlowEngine(state_dict, self.device, dt, config=config)
         self.cfg = self.model.cfg
 
     def validate_input_tensor(self, tensor):
