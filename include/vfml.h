@@ -250,6 +250,12 @@ int vfml_dwconv_tc_res_gelu(const void* x, void* y, int n_img, int h, int w, int
                             int64_t pitch_y, const void* packed, const float* bias, int k,
                             vfml_stream_t s);
 
+/* out[r, :n] = res[r, :n] + sum_s partial[s, r, :n]: combines split-K partial products (fp32, [n_splits, rows, n]
+ * contiguous) of the GMA aggregate `attn @ v` (gma.py:113) / MemFlow read-out (memory_manager_skflow.py:88-89) with the
+ * motion features (`fmap + gamma * out`, gma.py:115; gamma rides in the GEMM's alpha).  res may be NULL; n % 4 == 0. */
+int vfml_splitk_reduce(const float* partial, int n_splits, int64_t rows, int n, const void* res, int64_t ld_res,
+                       void* out, int64_t ld_out, int dtype, vfml_stream_t s);
+
 /* Row softmax in place-capable form: out[r, :] = softmax(in[r, :n]) (gma.py:74). in fp32. */
 int vfml_softmax_rows(const float* in, void* out, int64_t rows, int n, int64_t ld_in, int64_t ld_out,
                       int out_dtype, vfml_stream_t s);

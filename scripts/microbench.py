@@ -17,14 +17,20 @@ def buf(n, c, dtype=dt):
     return torch.randn((n, (c + 7) // 8 * 8), device=dev).to(dtype)[:, :c]
 
 
-def timeit(fn, reps=50):
-    for _ in range(5):
+def timeit(fn, reps=20):
+    """us per call, replayed from a CUDA graph (an eager ctypes launch costs ~12 us of CPU time, more than the small kernels)."""
+    for _ in range(3):
         fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(reps):
+            fn()
+    g.replay()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     e0.record()
-    for _ in range(reps):
-        fn()
+    g.replay()
     e1.record()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) / reps * 1000.0   # us
@@ -54,11 +60,23 @@ for name, M, C, Co, k in blocks:
         us = timeit(fn)
         total += us
         print(f"{label:44s} {us:9.1f} {flops / us / 1e6:9.1f}")
-# aggregate
-attn = torch.softmax(torch.randn((P, P), device=dev), -1).to(dt)
+# aggregate: one affinity matrix per centre frame (3 x 99 MB: cycles through HBM, as in the engine)
+attns = [torch.softmax(torch.randn((P, P), device=dev), -1).to(dt) for _ in range(Fc)]
 vT, mf, o = buf(128, P), buf(P, 128), buf(P, 128)
-us = timeit(lambda: ops.gemm(attn, vT, o, res=mf, alpha=0.5))
-print(f"{'aggregate attn.v (per frame) 7040x128x7040':44s} {us:9.1f} {2.0 * P * P * 128 / us / 1e6:9.1f}   x{Fc}")
+def agg_single():
+    for a_ in attns:
+        ops.gemm(a_, vT, o, res=mf, alpha=0.5)
+us = timeit(agg_single) / Fc
+print(f"{'aggregate attn.v (per frame) 7040x128x7040':44s} {us:9.1f} {2.0 * P * P * 128 / us / 1e6:9.1f}   x{Fc}  single pass")
+for S in (2, 5, 10):
+    part = torch.empty(S * P * 128, device=dev, dtype=torch.float32)
+    def agg_split():
+        for a_ in attns:
+            ops.gemm_splitk(a_, vT, o, S, part, res=mf, alpha=0.5)
+    us_s = timeit(agg_split) / Fc
+    print(f"{'  split-K ' + str(S) + ' + reduce':44s} {us_s:9.1f} {2.0 * P * P * 128 / us_s / 1e6:9.1f}   ({P * P * 2 / us_s / 1e6:.2f} TB/s of affinity rows)")
+    if S == 5:
+        us = us_s
 total += Fc * us
 wv = buf(128, 128)
 us = timeit(lambda: ops.gemm(wv, mf, vT))

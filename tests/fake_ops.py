@@ -125,6 +125,17 @@ def dwconv_res_gelu(x, y, n_img, h, w, weight_tapmajor, bias, k):
     return y
 
 
+def gemm_splitk(a, w, out, n_splits, partial, res=None, alpha=1.0):
+    Ks = a.shape[1] // n_splits
+    acc = torch.zeros(out.shape, dtype=torch.float32)
+    for s_ in range(n_splits):
+        acc += alpha * (a[:, s_ * Ks:(s_ + 1) * Ks].float() @ w[:, s_ * Ks:(s_ + 1) * Ks].float().t())
+    if res is not None:
+        acc += res.float()
+    out.copy_(acc.to(out.dtype))
+    return out
+
+
 def softmax_rows(src, dst):
     dst.copy_(torch.softmax(src, dim=-1).to(dst.dtype))
     return dst

@@ -446,3 +446,31 @@ def test_alt_corr_errors(ops):
         ops.alt_corr_forward(f.permute(0, 2, 1, 3), f, c, 4)
     with pytest.raises(RuntimeError, match="radius"):
         ops.alt_corr_forward(torch.zeros((1, 4, 4, 128), device="cuda"), torch.zeros((1, 4, 4, 128), device="cuda"), c, 5)
+
+
+# ---------------------------------------------------------------- split-K aggregate GEMM
+@pytest.mark.parametrize("M,K,N,S", [(7040, 7040, 128, 5), (1000, 1536, 128, 3), (384, 768, 128, 2)])
+def test_gemm_splitk_matches_single_pass(ops, M, K, N, S):
+    g = torch.Generator(device="cuda").manual_seed(M + K)
+    a = torch.softmax(4 * torch.randn((M, K), device="cuda", generator=g), -1).half()       # an affinity matrix
+    buf = torch.zeros((N, K + 8), device="cuda", dtype=torch.float16)
+    w = buf[:, :K]
+    w.copy_(torch.randn((N, K), device="cuda", generator=g).half())
+    res = rows_buf(M, N, torch.float16)
+    res.copy_(torch.randn((M, N), device="cuda", generator=g).half())
+    want = res.double() + 0.5 * (a.double() @ w.double().t())
+    out = rows_buf(M, 2 * N, torch.float16)[:, N:]                  # a column range of a wider buffer
+    part = torch.empty(S * M * N, device="cuda", dtype=torch.float32)
+    ops.gemm_splitk(a, w, out, S, part, res=res, alpha=0.5)
+    close(out, want, 2e-3, 1e-3)
+    one = rows_buf(M, N, torch.float16)
+    ops.gemm(a, w, one, res=res, alpha=0.5)
+    close(out, one, 2e-3, 1e-3)
+    with pytest.raises(ValueError):
+        ops.gemm_splitk(a, w, out, 7, part, res=res)
+
+
+def test_engine_split_factor():
+    from video_flow_ml_b200.mof import MOFEngine
+    assert MOFEngine._splits(7040, 7040) == 5 and MOFEngine._splits(7040, 14080) == 5
+    assert MOFEngine._splits(384, 384) == 1 and MOFEngine._splits(21600, 21600) == 1 and MOFEngine._splits(7040, 7000) == 1

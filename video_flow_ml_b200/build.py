@@ -15,7 +15,10 @@ LIB = os.path.join(HERE, "libvfml.so")
 STAMP = os.path.join(HERE, "build", "libvfml.stamp")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-         "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
+         "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"] + os.environ.get("VFML_NVCC_EXTRA", "").split()
+if os.environ.get("VFML_LIB_OUT"):        # experiment variants: VFML_NVCC_EXTRA=-DX=1 VFML_LIB_OUT=build/libvfml_x.so
+    LIB = os.path.abspath(os.environ["VFML_LIB_OUT"])
+    STAMP = LIB + ".stamp"
 
 
 def sources():

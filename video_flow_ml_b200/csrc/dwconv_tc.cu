@@ -199,7 +199,7 @@ dwconv_tc_kernel(const __half* __restrict__ x, __half* __restrict__ y, int h, in
                     const uint32_t xc = dt_lds32(a);
                     const float2 xf = __half22float2(*reinterpret_cast<const __half2*>(&xc));
                     float2 v = make_float2(xf.x + (acc[mb][s][hh * 2] + bv), xf.y + (acc[mb][s][hh * 2 + 1] + bv));
-                    v = gelu_poly2(v);
+                    v = gelu_fast2(v);
                     const __half2 o = __floats2half2_rn(v.x, v.y);
                     dt_sts32(a, *reinterpret_cast<const uint32_t*>(&o));
                 }

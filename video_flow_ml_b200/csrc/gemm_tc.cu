@@ -339,7 +339,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     }
                     if (do_gelu) {
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) x[i] = gelu_poly2(x[i]);
+                        for (int i = 0; i < 8; ++i) x[i] = gelu_fast2(x[i]);
                     }
                     if (do_relu) {
 #pragma unroll
@@ -357,7 +357,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                                 w2 = make_float2(__ldg(p.dw_w + n1), __ldg(p.dw_w + n2));
                                 b2 = make_float2(__ldg(p.dw_b + n1), __ldg(p.dw_b + n2));
                             }
-                            x[i] = gelu_poly2(add2(x[i], fma2(w2, x[i], b2)));
+                            x[i] = gelu_fast2(add2(x[i], fma2(w2, x[i], b2)));
                         }
                     }
                     if (p.out_f32) {

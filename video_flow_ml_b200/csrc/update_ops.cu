@@ -182,6 +182,31 @@ __global__ void __launch_bounds__(256) motion_glue_kernel(const GlueParams p) {
     }
 }
 
+// out[r, c] = res[r, c] + sum_s partial[s, r, c]: combines the split-K partial products of the aggregate GEMM
+// (gma.py:113-115 / memory read-out) with the residual.  One thread per 4 columns.
+template <typename T>
+__global__ void splitk_reduce_kernel(const float* __restrict__ partial, int S, int64_t M, int N, int64_t slab, const T* __restrict__ res,
+                                     int64_t ldr, T* __restrict__ out, int64_t ldo) {
+    const int n4 = N >> 2;
+    const int64_t total = M * n4;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = t / n4;
+        const int c = (int)(t - r * n4) << 2;
+        const float* pp = partial + r * N + c;
+        float4 acc = *reinterpret_cast<const float4*>(pp);
+        for (int s = 1; s < S; ++s) {
+            const float4 v = *reinterpret_cast<const float4*>(pp + s * slab);
+            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+        if (res) {
+            const T* rr = res + r * ldr + c;
+            acc.x += to_f32<T>(rr[0]); acc.y += to_f32<T>(rr[1]); acc.z += to_f32<T>(rr[2]); acc.w += to_f32<T>(rr[3]);
+        }
+        T* o = out + r * ldo + c;
+        o[0] = from_f32<T>(acc.x); o[1] = from_f32<T>(acc.y); o[2] = from_f32<T>(acc.z); o[3] = from_f32<T>(acc.w);
+    }
+}
+
 __global__ void coords_add_kernel(float* __restrict__ fc, float* __restrict__ bc, const float* __restrict__ delta,
                                   int64_t ld, int F, int hw) {
     const int64_t total = (int64_t)F * hw;
@@ -316,6 +341,20 @@ extern "C" int vfml_softmax_rows(const float* in, void* out, int64_t rows, int n
     DISPATCH_T(out_dtype, (softmax_rows_kernel<float><<<(unsigned)rows, 256, 0, to_stream(s)>>>(in, (float*)out, n, ld_in, ld_out)),
                (softmax_rows_kernel<__half><<<(unsigned)rows, 256, 0, to_stream(s)>>>(in, (__half*)out, n, ld_in, ld_out)));
     VFML_LAUNCH_CHECK("softmax_rows");
+    return VFML_OK;
+}
+
+extern "C" int vfml_splitk_reduce(const float* partial, int n_splits, int64_t rows, int n, const void* res, int64_t ld_res,
+                                  void* out, int64_t ld_out, int dtype, vfml_stream_t s) {
+    VFML_REQUIRE(n_splits >= 1 && rows >= 0 && n > 0 && (n % 4) == 0 && ld_out >= n && (!res || ld_res >= n), "splitk_reduce: bad shape (n %% 4 == 0)");
+    VFML_REQUIRE(valid_dtype(dtype), "splitk_reduce: bad dtype");
+    if (rows == 0) return VFML_OK;
+    VFML_REQUIRE(partial && out, "splitk_reduce: null pointer");
+    VFML_REQUIRE((reinterpret_cast<uintptr_t>(partial) & 15) == 0, "splitk_reduce: partial must be 16-byte aligned");
+    const int64_t total = rows * (n / 4), slab = rows * n;
+    DISPATCH_T(dtype, (splitk_reduce_kernel<float><<<ew_blocks(total), 256, 0, to_stream(s)>>>(partial, n_splits, rows, n, slab, (const float*)res, ld_res, (float*)out, ld_out)),
+               (splitk_reduce_kernel<__half><<<ew_blocks(total), 256, 0, to_stream(s)>>>(partial, n_splits, rows, n, slab, (const __half*)res, ld_res, (__half*)out, ld_out)));
+    VFML_LAUNCH_CHECK("splitk_reduce");
     return VFML_OK;
 }
 

@@ -180,7 +180,7 @@ class MemFlowEngine(MOFEngine):
         # value of the current frame (sk2.py:201-203), transposed straight into its memory slot; read-out + gamma
         vT = ws["vT"]
         o.gemm(self.w_v, mf, vT[:, 0:P])
-        o.gemm(ws["attn"][:, :T], vT[:, :T], x512[:, 384:512], res=mf, alpha=self.gamma)
+        self._aggregate(ws, ws["attn"][:, :T], vT[:, :T], mf, x512[:, 384:512])
         self._pcblock(x512, self.gru, ws, 1, h, w, [(full, full, x512[:, 0:128], None)])
         self._pcblock(x512[:, 0:128], self.fhead, ws, 1, h, w, [(full, full, ws["delta"][:, 0:2], None)])
         o.coords_add(c1, grid, ws["delta"])

@@ -155,6 +155,32 @@ class MOFEngine:
             raise RuntimeError("scratch buffer too small")
         return flat[: n * pitch].view(n, pitch)[:, :c]
 
+    # ------------------------------------------------------------------ aggregate
+    @staticmethod
+    def _splits(M, K):
+        """Split-K factor of the aggregate / read-out GEMM `attn [M, K] @ v [K, 128]`: its M / 128 row tiles (55 at
+        config C1) leave most of the 148 SMs idle while each busy SM streams 1.8 MB of attention rows, so K is cut into
+        S equal multiples of 64 until there are ~2 waves of CTAs.  1 = not worth it / not divisible."""
+        m_tiles = (M + 127) // 128
+        if K % 64 or m_tiles >= 148:
+            return 1
+        nkb = K // 64
+        for S in range(2, nkb + 1):
+            if nkb % S == 0 and K // S >= 512 and m_tiles * S >= 266:
+                return S
+        return 1
+
+    def _aggregate(self, ws, attn, vT, res, out):
+        """out = res + gamma * attn @ vT^T   (gma.py:113-115; memory read-out + inference_core_skflow.py:43)"""
+        M, K = attn.shape
+        S = self._splits(M, K) if hasattr(self.ops, "gemm_splitk") else 1
+        if S == 1:
+            return self.ops.gemm(attn, vT, out, res=res, alpha=self.gamma)
+        part = ws.get("partial")
+        if part is None or part.numel() < S * M * out.shape[1]:
+            part = ws["partial"] = torch.empty(S * M * out.shape[1], dtype=torch.float32, device=self.dev)
+        return self.ops.gemm_splitk(attn, vT, out, S, part, res=res, alpha=self.gamma)
+
     # ------------------------------------------------------------------ PCBlock
     def _pcblock(self, x, W, ws, n_img, h, w, outs):
         """x: rows view [M, Cin].  outs: list of (weight_row_slice, row_slice, out_view, act) for the
@@ -243,7 +269,7 @@ class MOFEngine:
             rows = slice(f * P, (f + 1) * P)
             vT = ws["vT"][f][:, :P]
             o.gemm(self.w_v, mf[rows], vT)                                   # to_v, transposed: [128, P]
-            o.gemm(ws["attn"][f][:, :P], vT, x512[rows, 384:512], res=mf[rows], alpha=self.gamma)
+            self._aggregate(ws, ws["attn"][f][:, :P], vT, mf[rows], x512[rows, 384:512])
         self._pcblock(x512, self.gru, ws, Fc, h, w, [(full, full, x512[:, 0:128], None)])
         self._pcblock(x512[:, 0:128], self.fhead, ws, Fc, h, w, [(full, full, ws["delta"], None)])
         o.coords_add(fc, bc, ws["delta"])

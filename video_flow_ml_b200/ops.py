@@ -425,6 +425,28 @@ def dwconv_tc_res_gelu(x, y, n_img, h, w, packed, bias, k):
     return y
 
 
+def gemm_splitk(a, w, out, n_splits, partial, res=None, alpha=1.0):
+    """out = res + alpha * a @ w^T with the K range cut into n_splits equal parts that run as the batch dimension of ONE
+    launch (more CTAs than row tiles: a [7040, 7040] x [7040, 128] aggregate has only 55 row tiles for 148 SMs),
+    partial products in `partial` (fp32, >= n_splits * M * N elements), combined by splitk_reduce."""
+    _cuda(a, w, out, partial, res)
+    _rows(a, "a"); _rows(w, "w"); _rows(out, "out")
+    M, K = a.shape
+    N = w.shape[0]
+    if K % n_splits or w.shape[1] != K or out.shape != (M, N) or partial.dtype != torch.float32 or partial.numel() < n_splits * M * N:
+        raise ValueError("gemm_splitk: shape mismatch")
+    Ks = K // n_splits
+    a3 = torch.as_strided(a, (n_splits, M, Ks), (Ks, a.stride(0), 1), a.storage_offset())
+    w3 = torch.as_strided(w, (n_splits, N, Ks), (Ks, w.stride(0), 1), w.storage_offset())
+    p3 = partial.reshape(-1)[: n_splits * M * N].view(n_splits, M, N)
+    gemm_batched(a3, w3, p3, alpha=alpha)
+    if res is not None:
+        _rows(res, "res")
+    _lib.check(_lib.load().vfml_splitk_reduce(_p(p3), n_splits, M, N, _p(res), res.stride(0) if res is not None else 0, _p(out),
+                                              out.stride(0), _dt(out), _stream()), "splitk_reduce")
+    return out
+
+
 def softmax_rows(src, dst):
     _cuda(src, dst)
     _rows(src, "src"); _rows(dst, "dst")
