@@ -234,7 +234,7 @@ def main():
     lk_ms = l0.elapsed_time(l1) / reps          # one launch = forward + backward lookup of one iteration
     es = 4 if eng.dt == torch.float32 else 2
     # DRAM bytes per launch of the roofline kernel on this workload, from the committed ncu --set full capture
-    NCU_TRAFFIC = {"corr_lookup_tiled_kernel": 74434048 + 4427776}
+    NCU_TRAFFIC = {"corr_lookup_tiled_kernel": 74438912 + 3937792}
     alg_bytes = 2 * Fc * P * (4 * 100 * es + 8 + 324 * es)   # per pixel-direction 100 texels/level read + coords + 324 written
     peak, peak_kind = peaks()
     achieved = alg_bytes / (lk_ms * 1e-3) / 1e9

@@ -202,6 +202,9 @@ int vfml_taa_init(const uint8_t* cur, double* out, int h, int w, vfml_stream_t s
 #define VFML_EPI_RELU 8u
 #define VFML_EPI_DW1 16u   /* then v = gelu(v + dw_w[n]*v + dw_b[n]): the k=1 depthwise stage of a PCBlock */
 #define VFML_EPI_ADDTO 32u /* out += v (fp32 out only) */
+#define VFML_EPI_WEIGHTS 64u /* B, bias, dw_w, dw_b are constants (layer weights), not outputs of preceding kernels on the
+                                stream: the kernel may fetch them while the preceding kernel is still draining
+                                (programmatic dependent launch).  Never changes results. */
 
 typedef struct vfml_gemm_desc {
     /* D[m, n] = epi(alpha * sum_k A[m, k] * B[n, k]),  m < M, n < N, k < K */

@@ -98,7 +98,7 @@ def convex_upsample8(flow, mask, out=None, crop=None, flow_is_coords=False):
     return out
 
 
-def gemm(a, w, out, bias=None, res=None, act=None, dw=None, alpha=1.0, addto=False, require_tc=False):
+def gemm(a, w, out, bias=None, res=None, act=None, dw=None, alpha=1.0, addto=False, require_tc=False, weights=False):
     v = alpha * (a.float() @ w.float().t())
     if bias is not None:
         v = v + bias

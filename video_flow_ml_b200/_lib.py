@@ -8,7 +8,7 @@ LIB_PATH = os.path.join(_HERE, "libvfml.so")
 
 F32, F16 = 0, 1
 NCHW, ROWS = 0, 1
-EPI_BIAS, EPI_RES, EPI_GELU, EPI_RELU, EPI_DW1, EPI_ADDTO = 1, 2, 4, 8, 16, 32
+EPI_BIAS, EPI_RES, EPI_GELU, EPI_RELU, EPI_DW1, EPI_ADDTO, EPI_WEIGHTS = 1, 2, 4, 8, 16, 32, 64
 
 vp, i32, i64, f32, f64, u32, sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_double, C.c_uint32, C.c_size_t
 

@@ -93,6 +93,7 @@ __device__ __forceinline__ uint32_t h22u(__half2 h) { return *reinterpret_cast<u
 template <bool F32MATH>
 __global__ void __launch_bounds__(TL_WARPS * 32, TL_CTAS_PER_SM)
 corr_lookup_tiled_kernel(const TiledParams p) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // lets a PDL-launched successor start its prologue
     extern __shared__ __align__(128) uint8_t tl_smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t ring = smem_u32(tl_smem) + warp * TL_WARP_BYTES;

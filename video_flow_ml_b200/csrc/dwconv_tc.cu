@@ -80,6 +80,7 @@ template <int K>
 __global__ void __launch_bounds__(256, 2)
 dwconv_tc_kernel(const __half* __restrict__ x, __half* __restrict__ y, int h, int w, int C, int64_t px, int64_t py,
                  const __half* __restrict__ packed, const float* __restrict__ bias, int tiles_x, int tiles_y) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // lets a PDL-launched successor start its prologue
     using Cfg = DtCfg<K>;
     constexpr int R = Cfg::R, INH = Cfg::INH, PLANE = Cfg::PLANE, WCH = Cfg::WCH;
     extern __shared__ __align__(128) uint8_t dt_smem[];

@@ -45,6 +45,7 @@ struct TcParams {
     int out_f32;
     int vec_in_smem;
     int b_res;           // weight-stationary mode: this CTA's B tile (all K blocks) stays in shared memory
+    int b_is_const;      // B (and bias / dw vectors) are weights: may be fetched before the preceding kernel has finished
     long long* trace;    // debug (VFML_GEMM_TRACE=1): per-CTA cycle counters, 8 per CTA
 };
 
@@ -127,6 +128,9 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const TcParams p) {
+    // programmatic dependent launch: the next kernel of the stream may start its prologue as soon as every CTA of this
+    // grid has got here (this grid is persistent, <= 1 CTA per SM: nothing of it is left to schedule)
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     const int BN = p.BN, stages = p.stages;
@@ -179,6 +183,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(512u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    if (!p.b_is_const) asm volatile("griddepcontrol.wait;" ::: "memory");     // bias / dw vectors may be activations
     if (p.vec_in_smem && warp >= 2) {
         for (int i = threadIdx.x - 64; i < vec_cols; i += TC_EPI_WARPS * 32) {
             const bool ok = i < p.N;
@@ -192,11 +197,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = tmem_base_s;
 
+    // Everything above (barriers, TMEM, bias / dw vectors) and the resident weight tile below depend on constants only;
+    // activations written by the preceding kernels are touched after griddepcontrol.wait.
+    if (warp == 0 && lane == 0 && p.b_res && p.b_is_const && t_first < t_end) {
+        mbar_expect_tx(&b_full, (uint32_t)nkb * b_bytes);
+        for (int kb = 0; kb < nkb; ++kb) tma_load_3d(&mapB, &b_full, sB + (size_t)kb * b_stride, kb * TC_BK, n_fixed, 0);
+    }
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+
     if (warp == 0) {
         if (lane == 0) {
             uint32_t it = 0;
             long long t_wait = 0, t0 = clock64();
-            if (p.b_res && t_first < t_end) {
+            if (p.b_res && !p.b_is_const && t_first < t_end) {
                 mbar_expect_tx(&b_full, (uint32_t)nkb * b_bytes);
                 for (int kb = 0; kb < nkb; ++kb) tma_load_3d(&mapB, &b_full, sB + (size_t)kb * b_stride, kb * TC_BK, n_fixed, 0);
             }
@@ -539,7 +552,26 @@ int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st) {
         VFML_CUDA(cudaMemsetAsync(trace_buf, 0, 148 * 8 * sizeof(long long), st));
         p.trace = trace_buf;
     }
-    gemm_tc_kernel<<<grid, TC_THREADS, smem, st>>>(mapA, mapB, p);
+    // programmatic dependent launch: this kernel's prologue (and its resident weight tile) overlaps the tail of the
+    // preceding kernel; it synchronises with griddepcontrol.wait before touching activations
+    static const bool no_pdl = getenv("VFML_NO_PDL") != nullptr;
+    p.b_is_const = (d.epi & VFML_EPI_WEIGHTS) != 0;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = no_pdl ? 0 : 1;
+    cudaError_t le = cudaLaunchKernelEx(&cfg, gemm_tc_kernel, mapA, mapB, p);
+    if (le != cudaSuccess) {
+        set_error("gemm_tc: launch failed: %s", cudaGetErrorString(le));
+        cudaGetLastError();
+        return VFML_ERR_CUDA;
+    }
     VFML_LAUNCH_CHECK("gemm_tc");
     if (trace) {      // debug only: synchronises
         long long h[148 * 8];

@@ -150,6 +150,7 @@ __device__ __forceinline__ void warp_state(const T* x400, int64_t p400, int fram
 
 template <typename T>
 __global__ void __launch_bounds__(256) motion_glue_kernel(const GlueParams p) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // lets a PDL-launched successor start its prologue
     const int lane = threadIdx.x & 31;
     const int P = p.h * p.w;
     const int64_t total = (int64_t)p.F * P;
@@ -187,6 +188,7 @@ __global__ void __launch_bounds__(256) motion_glue_kernel(const GlueParams p) {
 template <typename T>
 __global__ void splitk_reduce_kernel(const float* __restrict__ partial, int S, int64_t M, int N, int64_t slab, const T* __restrict__ res,
                                      int64_t ldr, T* __restrict__ out, int64_t ldo) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // lets a PDL-launched successor start its prologue
     const int n4 = N >> 2;
     const int64_t total = M * n4;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
@@ -209,6 +211,7 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ partial, int S, i
 
 __global__ void coords_add_kernel(float* __restrict__ fc, float* __restrict__ bc, const float* __restrict__ delta,
                                   int64_t ld, int F, int hw) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // lets a PDL-launched successor start its prologue
     const int64_t total = (int64_t)F * hw;
     for (int64_t row = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; row < total; row += (int64_t)gridDim.x * blockDim.x) {
         const int f = (int)(row / hw);

@@ -188,20 +188,20 @@ class MOFEngine:
         o = self.ops
         M = x.shape[0]
         t1 = self._view(ws["hid"], M, W.hid)
-        o.gemm(x, W.w1a, t1, bias=W.b1a, act="gelu")                                         # ffn1.0 + GELU
+        o.gemm(x, W.w1a, t1, bias=W.b1a, act="gelu", weights=True)                                         # ffn1.0 + GELU
         x2 = self._view(ws["sa"], M, W.cin)
-        o.gemm(t1, W.w1b, x2, bias=W.b1b, res=x, act="gelu", dw=(W.dw1_w, W.dw1_b))            # gelu(x+ffn1) ; k=1 dw stage
+        o.gemm(t1, W.w1b, x2, bias=W.b1b, res=x, act="gelu", dw=(W.dw1_w, W.dw1_b), weights=True)            # gelu(x+ffn1) ; k=1 dw stage
         x3 = self._view(ws["sb"], M, W.cin)
         if W.dwk_packed is not None:                                                           # gelu(x + dw_k(x))
             o.dwconv_tc_res_gelu(x2, x3, n_img, h, w, W.dwk_packed, W.dwk_b, W.k)
         else:
             o.dwconv_res_gelu(x2, x3, n_img, h, w, W.dwk_w, W.dwk_b, W.k)
         x4 = self._view(ws["sa"], M, W.cin)
-        o.gemm(x3, W.wpw, x4, bias=W.bpw, res=x3, act="gelu")                                  # gelu(x + pw(x))
+        o.gemm(x3, W.wpw, x4, bias=W.bpw, res=x3, act="gelu", weights=True)                                  # gelu(x + pw(x))
         t2 = self._view(ws["hid"], M, W.hid)
-        o.gemm(x4, W.w2a, t2, bias=W.b2a, act="gelu")                                          # ffn2.0 + GELU
+        o.gemm(x4, W.w2a, t2, bias=W.b2a, act="gelu", weights=True)                                          # ffn2.0 + GELU
         for wsl, rsl, out, act in outs:                                                         # ffn2.2
-            o.gemm(t2[rsl], W.w2b[wsl], out, bias=W.b2b[wsl].contiguous(), act=act)
+            o.gemm(t2[rsl], W.w2b[wsl], out, bias=W.b2b[wsl].contiguous(), act=act, weights=True)
 
     # ------------------------------------------------------------------ pieces
     @torch.no_grad()

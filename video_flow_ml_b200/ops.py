@@ -323,7 +323,7 @@ def taa(cur, flow, history, alpha, sigma_color, mode, hist_f32):
 
 
 # ------------------------------------------------------------------ update-step building blocks
-def gemm(a, w, out, bias=None, res=None, act=None, dw=None, alpha=1.0, addto=False, require_tc=False):
+def gemm(a, w, out, bias=None, res=None, act=None, dw=None, alpha=1.0, addto=False, require_tc=False, weights=False):
     """out[m, n] = epi(alpha * sum_k a[m, k] w[n, k]).  a, w, out, res: rows views."""
     _cuda(a, w, out, bias, res)
     _rows(a, "a"); _rows(w, "w"); _rows(out, "out")
@@ -356,6 +356,8 @@ def gemm(a, w, out, bias=None, res=None, act=None, dw=None, alpha=1.0, addto=Fal
         epi |= _lib.EPI_DW1
     if addto:
         epi |= _lib.EPI_ADDTO
+    if weights:           # w, bias, dw are layer constants: fetched while the preceding kernel drains
+        epi |= _lib.EPI_WEIGHTS
     d.epi = epi
     d.in_dtype, d.out_dtype = _dt(a), _dt(out)
     if require_tc and not _lib.load().vfml_gemm_uses_tensor_cores(C.byref(d)):
