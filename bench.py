@@ -165,6 +165,8 @@ def main():
     # ---- device-resident arm ("value")
     for i in range(warm):
         proc.core.compute_flow_from_tensor(windows[i % CLIP], out=out[i % n_steps])
+    if world > 1:      # untimed: NCCL sets up its point-to-point channels lazily, on the first gather
+        sharding.gather_flows(out, world * n_steps, world, rank, dst=0)
     barrier()
     sampler = ClockSampler(local)
     sampler.start()

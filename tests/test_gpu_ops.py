@@ -472,5 +472,5 @@ def test_gemm_splitk_matches_single_pass(ops, M, K, N, S):
 
 def test_engine_split_factor():
     from video_flow_ml_b200.mof import MOFEngine
-    assert MOFEngine._splits(7040, 7040) == 5 and MOFEngine._splits(7040, 14080) == 5
+    assert MOFEngine._splits(7040, 7040) == 2 and MOFEngine._splits(7040, 14080) == 2
     assert MOFEngine._splits(384, 384) == 1 and MOFEngine._splits(21600, 21600) == 1 and MOFEngine._splits(7040, 7000) == 1

@@ -15,6 +15,8 @@ Weights use the upstream checkpoint key names (``update_block.encoder.convc1.ffn
 <= 1e-2 px vs the fp32 reference) or float16 (tensor-core tier; the reference itself runs
 this part under fp16 autocast, network.py:149-192).
 """
+import os
+
 import torch
 
 from . import _lib
@@ -114,6 +116,7 @@ class MOFEngine:
         self.use_graph = use_graph
         self.lookup_math_f32 = False     # fp16x2 interpolation: 2.43e-2 px vs 2.37e-2 px (fp32) end to end, 8 % faster
         self.graph_launches = 0          # kernels executed through CUDA-graph replays (not seen by vfml_launch_count)
+        self.use_side_stream = os.environ.get("VFML_NO_SIDE_STREAM") is None
 
     # ------------------------------------------------------------------ buffers
     def _rows_buf(self, n, c, dtype=None):
@@ -137,6 +140,7 @@ class MOFEngine:
                 "sa": self._rows_buf(2 * Np, 512),
                 "sb": self._rows_buf(2 * Np, 512),
                 "hid": self._rows_buf(2 * Np, 768),
+                "hid2": self._rows_buf(Np, 192), "sa2": self._rows_buf(Np, 128), "sb2": self._rows_buf(Np, 128),   # side stream (convf2)
                 "qk": self._rows_buf(Np, 256),
                 "attn": torch.zeros((Fc, h * w, _pad8(h * w)), dtype=self.dt, device=self.dev),
                 "logits": torch.empty((h * w, h * w), dtype=torch.float32, device=self.dev),
@@ -155,18 +159,40 @@ class MOFEngine:
             raise RuntimeError("scratch buffer too small")
         return flat[: n * pitch].view(n, pitch)[:, :c]
 
+    # ------------------------------------------------------------------ side stream (fork / join inside the captured graph)
+    def _fork_side(self):
+        self._side_ctx = None
+        if self.dev.type != "cuda" or not getattr(self, "use_side_stream", True):
+            return
+        if getattr(self, "_side", None) is None:
+            self._side = torch.cuda.Stream(device=self.dev)
+        main = torch.cuda.current_stream(self.dev)
+        self._side.wait_stream(main)
+        self._side_ctx = torch.cuda.stream(self._side)
+        self._side_ctx.__enter__()
+
+    def _back_to_main(self):
+        if self._side_ctx is not None:
+            self._side_ctx.__exit__(None, None, None)
+
+    def _join_side(self):
+        if getattr(self, "_side_ctx", None) is not None:
+            torch.cuda.current_stream(self.dev).wait_stream(self._side)
+            self._side_ctx = None
+
     # ------------------------------------------------------------------ aggregate
     @staticmethod
     def _splits(M, K):
         """Split-K factor of the aggregate / read-out GEMM `attn [M, K] @ v [K, 128]`: its M / 128 row tiles (55 at
         config C1) leave most of the 148 SMs idle while each busy SM streams 1.8 MB of attention rows, so K is cut into
-        S equal multiples of 64 until there are ~2 waves of CTAs.  1 = not worth it / not divisible."""
+        S equal multiples of 64 until most SMs have a CTA (measured at C1: S = 2, 5, 10 -> 29, 30, 35 us against 40 us unsplit;
+        the partial sums cost S x 3.6 MB per frame).  1 = not worth it / not divisible."""
         m_tiles = (M + 127) // 128
         if K % 64 or m_tiles >= 148:
             return 1
         nkb = K // 64
         for S in range(2, nkb + 1):
-            if nkb % S == 0 and K // S >= 512 and m_tiles * S >= 266:
+            if nkb % S == 0 and K // S >= 512 and m_tiles * S >= 100:
                 return S
         return 1
 
@@ -182,11 +208,13 @@ class MOFEngine:
         return self.ops.gemm_splitk(attn, vT, out, S, part, res=res, alpha=self.gamma)
 
     # ------------------------------------------------------------------ PCBlock
-    def _pcblock(self, x, W, ws, n_img, h, w, outs):
+    def _pcblock(self, x, W, ws, n_img, h, w, outs, scratch=("hid", "sa", "sb")):
         """x: rows view [M, Cin].  outs: list of (weight_row_slice, row_slice, out_view, act) for the
-        last 1x1 conv, so that the reference's cat/split around the block costs nothing."""
+        last 1x1 conv, so that the reference's cat/split around the block costs nothing.
+        scratch: names of the three workspace buffers the block may use (a second set for the side stream)."""
         o = self.ops
         M = x.shape[0]
+        ws = {"hid": ws[scratch[0]], "sa": ws[scratch[1]], "sb": ws[scratch[2]]}
         t1 = self._view(ws["hid"], M, W.hid)
         o.gemm(x, W.w1a, t1, bias=W.b1a, act="gelu", weights=True)                                         # ffn1.0 + GELU
         x2 = self._view(ws["sa"], M, W.cin)
@@ -250,13 +278,19 @@ class MOFEngine:
         mf = x512[:, 256:384]
         o.motion_glue(fc, bc, x400, ws["f128"], mf, self.convf1_w, self.convf1_b, Fc, h, w)
         full = slice(None)
+        xin = ws["x256"] if self.arch == "bof" else x400
+        # the flow branch (convf2, stack.py:94-95) is independent of the correlation branch: it runs on a side stream and
+        # fills the partial last waves of the big convc1 / convc2 kernels
+        self._fork_side()
+        self._pcblock(ws["f128"], self.convf2, ws, Fc, h, w, [(full, full, xin[:, 192:256], None)], scratch=("hid2", "sa2", "sb2"))
+        self._back_to_main()
         # convc1 on forward and backward correlation (shared weights), gelu(cat) -> cor_in   stack.py:89-92
         self._pcblock(corr2, self.convc1, ws, 2 * Fc, h, w,
                       [(full, slice(0, Np), ws["cor_in"][:, 0:128], "gelu"),
                        (full, slice(Np, 2 * Np), ws["cor_in"][:, 128:256], "gelu")])
         xin = ws["x256"] if self.arch == "bof" else x400     # BOF has no hidden state: the glue's warps land in a scratch x400
         self._pcblock(ws["cor_in"], self.convc2, ws, Fc, h, w, [(full, full, xin[:, 0:192], None)])
-        self._pcblock(ws["f128"], self.convf2, ws, Fc, h, w, [(full, full, xin[:, 192:256], None)])
+        self._join_side()
         if self.arch == "bof":
             self._pcblock(xin, self.conv, ws, Fc, h, w, [(full, full, x512[:, 256:380], None)])     # sk2.py:55-56
         else:
