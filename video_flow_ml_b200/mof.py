@@ -160,25 +160,29 @@ class MOFEngine:
         return flat[: n * pitch].view(n, pitch)[:, :c]
 
     # ------------------------------------------------------------------ side stream (fork / join inside the captured graph)
-    def _fork_side(self):
+    def _fork_side(self, k=0):
+        """Following launches go to side stream k (ordered after everything issued on the main stream so far)."""
         self._side_ctx = None
         if self.dev.type != "cuda" or not getattr(self, "use_side_stream", True):
             return
-        if getattr(self, "_side", None) is None:
-            self._side = torch.cuda.Stream(device=self.dev)
-        main = torch.cuda.current_stream(self.dev)
-        self._side.wait_stream(main)
-        self._side_ctx = torch.cuda.stream(self._side)
+        sides = self.__dict__.setdefault("_sides", {})
+        if k not in sides:
+            sides[k] = torch.cuda.Stream(device=self.dev)
+        sides[k].wait_stream(torch.cuda.current_stream(self.dev))
+        self._side_ctx = torch.cuda.stream(sides[k])
         self._side_ctx.__enter__()
+        self.__dict__.setdefault("_forked", set()).add(k)
 
     def _back_to_main(self):
         if self._side_ctx is not None:
             self._side_ctx.__exit__(None, None, None)
-
-    def _join_side(self):
-        if getattr(self, "_side_ctx", None) is not None:
-            torch.cuda.current_stream(self.dev).wait_stream(self._side)
             self._side_ctx = None
+
+    def _join_side(self, k=0):
+        """The main stream waits for side stream k."""
+        if k in self.__dict__.get("_forked", ()):
+            torch.cuda.current_stream(self.dev).wait_stream(self._sides[k])
+            self._forked.discard(k)
 
     # ------------------------------------------------------------------ aggregate
     @staticmethod
@@ -196,15 +200,17 @@ class MOFEngine:
                 return S
         return 1
 
-    def _aggregate(self, ws, attn, vT, res, out):
-        """out = res + gamma * attn @ vT^T   (gma.py:113-115; memory read-out + inference_core_skflow.py:43)"""
+    def _aggregate(self, ws, attn, vT, res, out, slot=0):
+        """out = res + gamma * attn @ vT^T   (gma.py:113-115; memory read-out + inference_core_skflow.py:43).
+        slot: which partial-sum buffer to use (frames that run concurrently on different streams need their own)."""
         M, K = attn.shape
         S = self._splits(M, K) if hasattr(self.ops, "gemm_splitk") else 1
         if S == 1:
             return self.ops.gemm(attn, vT, out, res=res, alpha=self.gamma)
-        part = ws.get("partial")
+        key = f"partial{slot}"
+        part = ws.get(key)
         if part is None or part.numel() < S * M * out.shape[1]:
-            part = ws["partial"] = torch.empty(S * M * out.shape[1], dtype=torch.float32, device=self.dev)
+            part = ws[key] = torch.empty(S * M * out.shape[1], dtype=torch.float32, device=self.dev)
         return self.ops.gemm_splitk(attn, vT, out, S, part, res=res, alpha=self.gamma)
 
     # ------------------------------------------------------------------ PCBlock
@@ -299,11 +305,19 @@ class MOFEngine:
                           [(slice(0, 124), full, x512[:, 256:380], None),
                            (slice(124, 172), full, x400[:, 352:400], None)])
         # Aggregate (gma.py:102-115): mfg = mf + gamma * attn @ to_v(mf)
-        for f in range(Fc):
+        # the centre frames are independent and each one's kernels fill well under 148 SMs (55 / 110 CTAs):
+        # frame 0 stays on the main stream, the others run beside it
+        for f in list(range(1, Fc)) + [0]:          # side frames first: a fork orders the side stream after the main stream's past
             rows = slice(f * P, (f + 1) * P)
             vT = ws["vT"][f][:, :P]
+            if f:
+                self._fork_side(f)
             o.gemm(self.w_v, mf[rows], vT)                                   # to_v, transposed: [128, P]
-            self._aggregate(ws, ws["attn"][f][:, :P], vT, mf[rows], x512[rows, 384:512])
+            self._aggregate(ws, ws["attn"][f][:, :P], vT, mf[rows], x512[rows, 384:512], slot=f)
+            if f:
+                self._back_to_main()
+        for f in range(1, Fc):
+            self._join_side(f)
         self._pcblock(x512, self.gru, ws, Fc, h, w, [(full, full, x512[:, 0:128], None)])
         self._pcblock(x512[:, 0:128], self.fhead, ws, Fc, h, w, [(full, full, ws["delta"], None)])
         o.coords_add(fc, bc, ws["delta"])
