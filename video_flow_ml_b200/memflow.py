@@ -17,6 +17,7 @@ What is different from the reference and does not change results:
 The update step reuses the MOF engine's PC-block driver, tiled correlation pyramid / lookup and CUDA-graph replay.
 """
 import math
+import os
 
 import torch
 
@@ -85,6 +86,7 @@ class MemFlowEngine(MOFEngine):
         self.use_graph = use_graph
         self.lookup_math_f32 = False
         self.graph_launches = 0
+        self.use_side_stream = os.environ.get("VFML_NO_SIDE_STREAM") is None
         self.clear_memory()
 
     # ------------------------------------------------------------------ memory (MemoryManager + KeyValueMemoryStore)
@@ -133,6 +135,7 @@ class MemFlowEngine(MOFEngine):
                 "sa": self._rows_buf(P, 512),
                 "sb": self._rows_buf(P, 512),
                 "hid": self._rows_buf(P, 9 * 128),
+                "hid2": self._rows_buf(P, 192), "sa2": self._rows_buf(P, 128), "sb2": self._rows_buf(P, 128),   # side stream (convf2)
                 "mask": self._rows_buf(P, 576, torch.float32),
                 "graphs": {},
             }
@@ -145,8 +148,13 @@ class MemFlowEngine(MOFEngine):
     def encode(self, images):
         """images [1, 2, 3, H, W] in [-1, 1] -> fmaps [2,256,h,w], net, inp [1,128,h,w]   (MemFlow.py:66-128)"""
         x = images.float()
-        fmaps = self.fnet(x[0])
+        self._fork_side()                                   # the context encoder runs beside the feature encoder
         cnet = self.cnet(x[:, 0])
+        self._back_to_main()
+        fmaps = self.fnet(x[0])
+        self._join_side()
+        if cnet.is_cuda:
+            cnet.record_stream(torch.cuda.current_stream(cnet.device))
         net, inp = torch.split(cnet, [128, 128], dim=1)
         return fmaps, torch.tanh(net).contiguous(), torch.relu(inp).contiguous()
 
@@ -166,16 +174,20 @@ class MemFlowEngine(MOFEngine):
         o = self.ops
         P = h * w
         x512, x256 = ws["x512"], ws["x256"]
+        mf = x512[:, 256:384]
+        full = slice(None)
+        # flow branch (sk2.py:102-103) on a side stream beside the correlation branch (sk2.py:98-100)
+        self._fork_side()
+        o.motion_glue(grid, c1, ws["x400"], ws["f128"], mf, self.convf1_w, self.convf1_b, 1, h, w)   # convf1 + flow -> mf[:, 126:128]
+        self._pcblock(ws["f128"], self.convf2, ws, 1, h, w, [(full, full, x256[:, 192:256], None)], scratch=("hid2", "sa2", "sb2"))
+        self._back_to_main()
         if self.tiled:
             o.corr_lookup_tiled(pyr, None, c1, None, ws["corr"], None, math_f32=self.lookup_math_f32)
         else:
             o.corr_lookup(pyr, c1, 4, out=ws["corr"])
-        mf = x512[:, 256:384]
-        o.motion_glue(grid, c1, ws["x400"], ws["f128"], mf, self.convf1_w, self.convf1_b, 1, h, w)   # convf1 + flow -> mf[:, 126:128]
-        full = slice(None)
         self._pcblock(ws["corr"], self.convc1, ws, 1, h, w, [(full, full, ws["cor_in"], "gelu")])     # sk2.py:98
         self._pcblock(ws["cor_in"], self.convc2, ws, 1, h, w, [(full, full, x256[:, 0:192], None)])
-        self._pcblock(ws["f128"], self.convf2, ws, 1, h, w, [(full, full, x256[:, 192:256], None)])
+        self._join_side()
         self._pcblock(x256, self.conv, ws, 1, h, w, [(full, full, x512[:, 256:382], None)])           # 126 + flow 2
         # value of the current frame (sk2.py:201-203), transposed straight into its memory slot; read-out + gamma
         vT = ws["vT"]

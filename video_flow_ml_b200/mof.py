@@ -244,8 +244,13 @@ class MOFEngine:
         network.py:144-170 (the 2*(x/255)-1 normalisation stays inside)."""
         B, T, _, H, W = images.shape
         x = 2 * (images.float() / 255.0) - 1.0
-        fmaps = self.fnet(x.reshape(B * T, 3, H, W))
+        self._fork_side()                                   # the context encoder runs beside the feature encoder
         cnet = self.cnet(x[:, 1:T - 1].reshape(B * (T - 2), 3, H, W))
+        self._back_to_main()
+        fmaps = self.fnet(x.reshape(B * T, 3, H, W))
+        self._join_side()
+        if cnet.is_cuda:
+            cnet.record_stream(torch.cuda.current_stream(cnet.device))
         net, inp = torch.split(cnet, [128, 128], dim=1)
         return fmaps, torch.tanh(net).contiguous(), torch.relu(inp).contiguous()
 
@@ -277,19 +282,19 @@ class MOFEngine:
         P = h * w
         Np = Fc * P
         corr2, x400, x512 = ws["corr2"], ws["x400"], ws["x512"]
+        mf = x512[:, 256:384]
+        full = slice(None)
+        xin = ws["x256"] if self.arch == "bof" else x400
+        # the flow branch (glue + convf2, stack.py:81-87,94-95) is independent of the correlation branch: it runs on a side
+        # stream and fills the partial last waves of the big convc1 / convc2 kernels
+        self._fork_side()
+        o.motion_glue(fc, bc, x400, ws["f128"], mf, self.convf1_w, self.convf1_b, Fc, h, w)
+        self._pcblock(ws["f128"], self.convf2, ws, Fc, h, w, [(full, full, xin[:, 192:256], None)], scratch=("hid2", "sa2", "sb2"))
+        self._back_to_main()
         if self.tiled:
             o.corr_lookup_tiled(fpyr, bpyr, fc, bc, corr2[:Np], corr2[Np:], math_f32=self.lookup_math_f32)
         else:
             o.corr_lookup_pair(fpyr, bpyr, fc, bc, corr2[:Np], corr2[Np:])
-        mf = x512[:, 256:384]
-        o.motion_glue(fc, bc, x400, ws["f128"], mf, self.convf1_w, self.convf1_b, Fc, h, w)
-        full = slice(None)
-        xin = ws["x256"] if self.arch == "bof" else x400
-        # the flow branch (convf2, stack.py:94-95) is independent of the correlation branch: it runs on a side stream and
-        # fills the partial last waves of the big convc1 / convc2 kernels
-        self._fork_side()
-        self._pcblock(ws["f128"], self.convf2, ws, Fc, h, w, [(full, full, xin[:, 192:256], None)], scratch=("hid2", "sa2", "sb2"))
-        self._back_to_main()
         # convc1 on forward and backward correlation (shared weights), gelu(cat) -> cor_in   stack.py:89-92
         self._pcblock(corr2, self.convc1, ws, 2 * Fc, h, w,
                       [(full, slice(0, Np), ws["cor_in"][:, 0:128], "gelu"),
