@@ -259,6 +259,12 @@ int vfml_dwconv_tc_res_gelu(const void* x, void* y, int n_img, int h, int w, int
 int vfml_splitk_reduce(const float* partial, int n_splits, int64_t rows, int n, const void* res, int64_t ld_res,
                        void* out, int64_t ld_out, int dtype, vfml_stream_t s);
 
+/* y[r, :C] = LayerNorm(x[r, :C]) * gamma + beta over rows buffers (x, y, gamma, beta of `dtype`, fp32 statistics).
+ * Replaces nn.LayerNorm of the Twins blocks (VideoFlow/core/Networks/twins_ft.py norm1 / norm2 of Block, eps 1e-6),
+ * the first native piece of SURVEY 8(f) n1.  C a multiple of 8 (fp16) / 4 (fp32), C <= 1024 (fp16) / 512 (fp32). */
+int vfml_layer_norm_rows(const void* x, void* y, int64_t rows, int C, int64_t ld_x, int64_t ld_y, const void* gamma,
+                         const void* beta, float eps, int dtype, vfml_stream_t s);
+
 /* Row softmax in place-capable form: out[r, :] = softmax(in[r, :n]) (gma.py:74). in fp32. */
 int vfml_softmax_rows(const float* in, void* out, int64_t rows, int n, int64_t ld_in, int64_t ld_out,
                       int out_dtype, vfml_stream_t s);

@@ -474,3 +474,22 @@ def test_engine_split_factor():
     from video_flow_ml_b200.mof import MOFEngine
     assert MOFEngine._splits(7040, 7040) == 2 and MOFEngine._splits(7040, 14080) == 2
     assert MOFEngine._splits(384, 384) == 1 and MOFEngine._splits(21600, 21600) == 1 and MOFEngine._splits(7040, 7000) == 1
+
+
+# ---------------------------------------------------------------- LayerNorm (Twins blocks)
+@pytest.mark.parametrize("dt,tol", [(torch.float32, 2e-6), (torch.float16, 2e-3)])
+@pytest.mark.parametrize("shape", [(5, 1000, 128), (3, 77, 256), (1, 9, 64), (2, 33, 320), (1, 5, 512)])
+def test_layer_norm_rows_matches_torch(ops, dt, tol, shape):
+    g = torch.Generator(device="cuda").manual_seed(shape[1])
+    x = (3 * torch.randn(shape, device="cuda", generator=g) + 1.5).to(dt)
+    w = (1 + 0.2 * torch.randn(shape[-1], device="cuda", generator=g)).to(dt)
+    b = (0.3 * torch.randn(shape[-1], device="cuda", generator=g)).to(dt)
+    want = torch.nn.functional.layer_norm(x.double(), (shape[-1],), w.double(), b.double(), 1e-6)
+    got = ops.layer_norm_rows(x, w, b, 1e-6)
+    assert got.shape == x.shape and got.dtype == dt
+    close(got, want, tol * 4, tol)
+    with pytest.raises(ValueError):
+        ops.layer_norm_rows(x.transpose(1, 2), w, b, 1e-6)
+    with pytest.raises(RuntimeError):
+        ops.layer_norm_rows(torch.zeros((4, 10), device="cuda", dtype=dt), torch.ones(10, device="cuda", dtype=dt),
+                            torch.zeros(10, device="cuda", dtype=dt), 1e-6)

@@ -209,6 +209,64 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ partial, int S, i
     }
 }
 
+// LayerNorm over the last dimension of a rows buffer (Twins blocks: twins_ft.py norm1 / norm2, C = 128 or 256): one warp
+// per row, the row lives in registers (VPL 8-element vectors per lane), two-pass mean / variance in fp32 like torch.
+template <typename T, int VPL>
+__global__ void __launch_bounds__(256) layer_norm_rows_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t rows, int C, int64_t ldx,
+                                                              int64_t ldy, const T* __restrict__ gamma, const T* __restrict__ beta, float eps) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5, nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    constexpr int E = 16 / (int)sizeof(T);        // elements per 16-byte vector
+    for (int64_t r = warp0; r < rows; r += nwarps) {
+        float v[VPL * E];
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int c = (i * 32 + lane) * E;
+            if (c < C) {
+                const uint4 q = *reinterpret_cast<const uint4*>(x + r * ldx + c);
+                const T* e = reinterpret_cast<const T*>(&q);
+#pragma unroll
+                for (int j = 0; j < E; ++j) v[i * E + j] = to_f32<T>(e[j]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < E; ++j) v[i * E + j] = 0.f;
+            }
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < VPL * E; ++i) s += v[i];
+#pragma unroll
+        for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        const float mean = s / (float)C;
+        float q2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int c = (i * 32 + lane) * E;
+            if (c < C) {
+#pragma unroll
+                for (int j = 0; j < E; ++j) { const float d = v[i * E + j] - mean; q2 += d * d; }
+            }
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) q2 += __shfl_xor_sync(0xffffffffu, q2, o);
+        const float rstd = rsqrtf(q2 / (float)C + eps);
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int c = (i * 32 + lane) * E;
+            if (c < C) {
+                const uint4 g4 = *reinterpret_cast<const uint4*>(gamma + c), b4 = *reinterpret_cast<const uint4*>(beta + c);
+                const T* g = reinterpret_cast<const T*>(&g4);
+                const T* b = reinterpret_cast<const T*>(&b4);
+                uint4 o4;
+                T* o = reinterpret_cast<T*>(&o4);
+#pragma unroll
+                for (int j = 0; j < E; ++j) o[j] = from_f32<T>((v[i * E + j] - mean) * rstd * to_f32<T>(g[j]) + to_f32<T>(b[j]));
+                *reinterpret_cast<uint4*>(y + r * ldy + c) = o4;
+            }
+        }
+    }
+}
+
 __global__ void coords_add_kernel(float* __restrict__ fc, float* __restrict__ bc, const float* __restrict__ delta,
                                   int64_t ld, int F, int hw) {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // lets a PDL-launched successor start its prologue
@@ -358,6 +416,34 @@ extern "C" int vfml_splitk_reduce(const float* partial, int n_splits, int64_t ro
     DISPATCH_T(dtype, (splitk_reduce_kernel<float><<<ew_blocks(total), 256, 0, to_stream(s)>>>(partial, n_splits, rows, n, slab, (const float*)res, ld_res, (float*)out, ld_out)),
                (splitk_reduce_kernel<__half><<<ew_blocks(total), 256, 0, to_stream(s)>>>(partial, n_splits, rows, n, slab, (const __half*)res, ld_res, (__half*)out, ld_out)));
     VFML_LAUNCH_CHECK("splitk_reduce");
+    return VFML_OK;
+}
+
+extern "C" int vfml_layer_norm_rows(const void* x, void* y, int64_t rows, int C, int64_t ld_x, int64_t ld_y, const void* gamma,
+                                    const void* beta, float eps, int dtype, vfml_stream_t s) {
+    VFML_REQUIRE(valid_dtype(dtype), "layer_norm_rows: bad dtype");
+    const int E = dtype == VFML_F16 ? 8 : 4;
+    VFML_REQUIRE(rows >= 0 && C > 0 && (C % E) == 0 && C <= 32 * 4 * E && ld_x >= C && ld_y >= C && (ld_x % E) == 0 && (ld_y % E) == 0,
+                 "layer_norm_rows: C must be a multiple of %d and <= %d, pitches multiples of %d", E, 32 * 4 * E, E);
+    if (rows == 0) return VFML_OK;
+    VFML_REQUIRE(x && y && gamma && beta, "layer_norm_rows: null pointer");
+    auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+    VFML_REQUIRE(al(x) && al(y) && al(gamma) && al(beta), "layer_norm_rows: pointers must be 16-byte aligned");
+    const int vpl = (C / E + 31) / 32;           // 16-byte vectors per lane
+    const int blocks = (int)std::min<int64_t>(cdiv(rows, 8), 148 * 16);
+#define VFML_LN_CASE(V)                                                                                                             \
+    case V:                                                                                                                         \
+        DISPATCH_T(dtype, (layer_norm_rows_kernel<float, V><<<blocks, 256, 0, to_stream(s)>>>((const float*)x, (float*)y, rows, C, ld_x, ld_y, (const float*)gamma, (const float*)beta, eps)), \
+                   (layer_norm_rows_kernel<__half, V><<<blocks, 256, 0, to_stream(s)>>>((const __half*)x, (__half*)y, rows, C, ld_x, ld_y, (const __half*)gamma, (const __half*)beta, eps))); \
+        break;
+    switch (vpl) {
+        VFML_LN_CASE(1)
+        VFML_LN_CASE(2)
+        VFML_LN_CASE(3)
+        VFML_LN_CASE(4)
+    }
+#undef VFML_LN_CASE
+    VFML_LAUNCH_CHECK("layer_norm_rows");
     return VFML_OK;
 }
 

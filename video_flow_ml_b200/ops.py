@@ -449,6 +449,19 @@ def gemm_splitk(a, w, out, n_splits, partial, res=None, alpha=1.0):
     return out
 
 
+def layer_norm_rows(x, weight, bias, eps):
+    """LayerNorm over the last dimension of a contiguous [..., C] tensor (fp32 or fp16, fp32 statistics)."""
+    _cuda(x, weight, bias)
+    if not x.is_contiguous() or x.dtype != weight.dtype or x.dtype != bias.dtype:
+        raise ValueError("layer_norm_rows: x must be contiguous, weight / bias of the same dtype")
+    Cc = x.shape[-1]
+    y = torch.empty_like(x)
+    rows = x.numel() // Cc
+    _lib.check(_lib.load().vfml_layer_norm_rows(_p(x), _p(y), rows, Cc, Cc, Cc, _p(weight), _p(bias), float(eps), _dt(x), _stream()),
+               "layer_norm_rows")
+    return y
+
+
 def softmax_rows(src, dst):
     _cuda(src, dst)
     _rows(src, "src"); _rows(dst, "dst")

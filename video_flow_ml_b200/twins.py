@@ -20,6 +20,11 @@ _PATCH = (4, 2)
 _WS = 7
 
 
+def _ops():
+    from . import ops
+    return ops
+
+
 class TwinsStage01:
     def __init__(self, state_dict, prefix, device, dtype=torch.float32):
         n = len(prefix) + 1
@@ -28,7 +33,10 @@ class TwinsStage01:
         self.dtype = dtype
 
     def _ln(self, x, name, eps):
-        return F.layer_norm(x, (x.shape[-1],), self.p[name + ".weight"], self.p[name + ".bias"], eps)
+        w, b = self.p[name + ".weight"], self.p[name + ".bias"]
+        if x.is_cuda and x.dtype == w.dtype and x.shape[-1] % 8 == 0 and x.shape[-1] <= 512:
+            return _ops().layer_norm_rows(x.contiguous(), w, b, eps)      # libvfml kernel; strided views are packed first, as torch does
+        return F.layer_norm(x, (x.shape[-1],), w, b, eps)
 
     def _fc(self, x, name):
         return F.linear(x, self.p[name + ".weight"], self.p.get(name + ".bias"))
