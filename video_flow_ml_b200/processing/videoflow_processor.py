@@ -6,6 +6,14 @@ import torch
 from .videoflow_core import VideoFlowCore
 
 
+class _NoEvent:
+    def record(self):
+        pass
+
+    def synchronize(self):
+        pass
+
+
 class VideoFlowProcessor:
     def __init__(self, device, fast_mode=False, tile_mode=False, sequence_length=5,
                  dataset='sintel', architecture='mof', variant='standard', precision=None):
@@ -54,13 +62,32 @@ class VideoFlowProcessor:
         through (reference :152-162)."""
         ids = self.window_indices(len(frames), frame_idx)
         seq = [frames[i] for i in ids]
-        if all(f.dtype == np.uint8 for f in seq):
-            # one u8 upload, conversion on the device (same fp32 division as the reference's numpy one)
-            u8 = torch.from_numpy(np.stack(seq)).to(self.device, non_blocking=True)
+        if all(f.dtype == np.uint8 for f in seq) and len({f.shape for f in seq}) == 1:
+            # one u8 upload from a pinned staging buffer (two buffers alternate; a buffer is rewritten only after the
+            # copy that last read it has finished), conversion on the device (same fp32 division as the reference's numpy one)
+            u8 = self._stage_u8(seq).to(self.device, non_blocking=True)
+            self._stage_events[self._stage_i].record()
             return (u8.permute(0, 3, 1, 2).float() / 255.0).unsqueeze(0)
         tensors = [torch.from_numpy((f.astype(np.float32) / 255.0) if f.dtype == np.uint8 else f.astype(np.float32)).permute(2, 0, 1)
                    for f in seq]
         return torch.stack(tensors).unsqueeze(0).to(self.device)
+
+    def _stage_u8(self, seq):
+        """Copies the window's frames into one of two pinned [T, H, W, 3] uint8 staging tensors."""
+        shape = (len(seq),) + tuple(seq[0].shape)
+        st = getattr(self, "_stage", None)
+        if st is None or tuple(st[0].shape) != shape:
+            pin = str(self.device).startswith("cuda") and torch.cuda.is_available()
+            self._stage = st = [torch.empty(shape, dtype=torch.uint8, pin_memory=pin) for _ in range(2)]
+            self._stage_np = [t.numpy() for t in st]
+            self._stage_events = [torch.cuda.Event() for _ in range(2)] if pin else [_NoEvent(), _NoEvent()]
+            self._stage_i = 0
+        self._stage_i ^= 1
+        self._stage_events[self._stage_i].synchronize()
+        dst = self._stage_np[self._stage_i]
+        for i, f in enumerate(seq):
+            np.copyto(dst[i], f)
+        return st[self._stage_i]
 
     # ------------------------------------------------------------------ inference
     def compute_optical_flow(self, frames, frame_idx):
