@@ -207,8 +207,10 @@ class InferenceCore:
     is a pair of [1,128,n*P] tensors; when it reaches max_mid_term_frames*P elements it is cut back to the last
     min_mid_term_frames*P (memory_manager_skflow.py:117-124, kv_memory_store.py:62-76)."""
 
-    def __init__(self, sd, iters=ITERS, mem_every=1, train_avg_length=TRAIN_AVG_LENGTH):
+    def __init__(self, sd, iters=ITERS, mem_every=1, train_avg_length=TRAIN_AVG_LENGTH, max_frames=MAX_MID_TERM_FRAMES,
+                 min_frames=MIN_MID_TERM_FRAMES):
         self.sd, self.iters, self.mem_every, self.tal = sd, iters, mem_every, train_avg_length
+        self.max_frames, self.min_frames = max_frames, min_frames
         self.clear_memory()
 
     def clear_memory(self):
@@ -246,9 +248,9 @@ class InferenceCore:
             self.mem_k = kf if self.mem_k is None else torch.cat([self.mem_k, kf], -1)
             self.mem_v = vf if self.mem_v is None else torch.cat([self.mem_v, vf], -1)
             P = h * w
-            if self.mem_k.shape[-1] >= MAX_MID_TERM_FRAMES * P:
-                self.mem_k = self.mem_k[:, :, -MIN_MID_TERM_FRAMES * P:]
-                self.mem_v = self.mem_v[:, :, -MIN_MID_TERM_FRAMES * P:]
+            if self.mem_k.shape[-1] >= self.max_frames * P:
+                self.mem_k = self.mem_k[:, :, -self.min_frames * P:]
+                self.mem_v = self.mem_v[:, :, -self.min_frames * P:]
             self.last_mem_ti = self.curr_ti
         return coords1 - coords0, flow_up
 

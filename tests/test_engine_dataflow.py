@@ -96,3 +96,25 @@ def test_memflow_engine_dataflow_matches_oracle():
     assert (gu - wu).abs().max() < 2e-3
     with pytest.raises(ValueError):
         eng.step(x[:, 0:3])
+
+
+@pytest.mark.parametrize("max_f,min_f,every", [(3, 2, 1), (2, 1, 2), (4, 1, 1)])
+def test_memflow_memory_policy_variants(max_f, min_f, every):
+    """Working-memory bookkeeping for other configs than the shipped 2 / 1 / 1 (memory_manager_skflow.py:99-124,
+    inference_core_skflow.py:24): frames stored, compression to the newest `min` frames, mem_every."""
+    from oracle import memflow as omem
+    from video_flow_ml_b200.memflow import MemFlowEngine
+    sd = omem.memflow_synthetic_weights(0)
+    frames = cases.mof_case()
+    x = torch.stack([torch.from_numpy(f).permute(2, 0, 1) for f in frames[:6]])[None]
+    x = omof.pad_frames(2 * (x / 255.0) - 1.0).contiguous()
+    want = omem.InferenceCore(sd, iters=2, mem_every=every, max_frames=max_f, min_frames=min_f)
+    eng = MemFlowEngine(sd, "cpu", torch.float32, ops=fake_ops, tiled=False,
+                        config={"val_decoder_depth": 2, "mem_every": every, "max_mid_term_frames": max_f, "min_mid_term_frames": min_f})
+    P = 16 * 24
+    for t in range(5):
+        wl, wu = want.step(x[:, t:t + 2])
+        gl, gu = eng.step(x[:, t:t + 2])
+        assert (gu - wu).abs().max() < 2e-3, (t, (gu - wu).abs().max())
+        stored = 0 if want.mem_k is None else want.mem_k.shape[-1] // P
+        assert eng.n_stored == stored, (t, eng.n_stored, stored)

@@ -213,3 +213,24 @@ def test_memflow_matches_reference_golden(golden, precision, tol):
     want = core.compute_flow_from_tensor(p.prepare_frame_sequence(u8, 3)).permute(1, 2, 0).numpy()
     assert np.array_equal(out, want)
     assert p.calculate_tile_grid(188, 124)[2:4] == (1, 1)
+
+
+def test_device_resident_post_pass(processor_g10):
+    """flow -> gamedev encode -> TAA without the D2H -> numpy hop of flow_processor.py:976-1112 gives
+    bit-identical results to the host-array path (the kernels are the same; only the copies disappear)."""
+    from video_flow_ml_b200.effects import TAAProcessor
+    from video_flow_ml_b200.encoding import encode_flow
+    frames = [np.clip(f, 0, 255).astype(np.uint8) for f in cases.mof_case()]
+    H, W = frames[0].shape[:2]
+    host_taa, dev_taa = TAAProcessor(alpha=0.1), TAAProcessor(alpha=0.1)
+    for idx in (2, 3):
+        flow_np = processor_g10.compute_optical_flow(frames, idx)
+        flow_dev = processor_g10.compute_optical_flow(frames, idx, return_device=True)
+        assert flow_dev.is_cuda and flow_dev.shape == (H, W, 2)
+        assert np.array_equal(flow_dev.cpu().numpy(), flow_np)
+        enc_np = encode_flow(flow_np, W, H, 'gamedev')
+        enc_dev = encode_flow(flow_dev, W, H, 'gamedev')
+        assert enc_dev.is_cuda and enc_dev.dtype == torch.uint8 and np.array_equal(enc_dev.cpu().numpy(), enc_np)
+        out_np = host_taa.apply_taa(enc_np, flow_np)
+        out_dev = dev_taa.apply_taa(enc_dev, flow_dev, return_device=True)
+        assert out_dev.is_cuda and np.array_equal(out_dev.cpu().numpy().astype(out_np.dtype), out_np)

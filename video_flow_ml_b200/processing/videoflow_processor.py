@@ -90,10 +90,15 @@ class VideoFlowProcessor:
         return st[self._stage_i]
 
     # ------------------------------------------------------------------ inference
-    def compute_optical_flow(self, frames, frame_idx):
+    def compute_optical_flow(self, frames, frame_idx, return_device=False):
+        """-> np.float32 [H, W, 2] like the reference (:164-187).  return_device=True keeps the [H, W, 2] flow on the GPU
+        (a view of the kernel's [2, H, W] output) for the device-resident post-pass: encoding.encode_flow and
+        effects.TAAProcessor accept CUDA tensors, so flow -> encode -> TAA needs no host round trip."""
         if not self.core.is_model_loaded():
             raise RuntimeError("Model not loaded. Call load_model() first.")
         flow = self.core.compute_flow_from_tensor(self.prepare_frame_sequence(frames, frame_idx))
+        if return_device:
+            return flow.permute(1, 2, 0)
         return flow.permute(1, 2, 0).cpu().numpy()
 
     def compute_optical_flow_with_progress(self, frames, frame_idx, tile_pbar=None):
@@ -116,12 +121,12 @@ class VideoFlowProcessor:
             tile_pbar.update(1)
         return flow_np
 
-    def compute_optical_flow_tiled(self, frames, frame_idx, tile_pbar=None, overall_pbar=None):
+    def compute_optical_flow_tiled(self, frames, frame_idx, tile_pbar=None, overall_pbar=None, return_device=False):
         """Disjoint 1280x1280 tiles, each an independent clip, pasted without blending (reference :231-283).
         Tiles are cropped from the window's frames only and each tile's flow is written by the upsampling
         kernel straight into the full-frame device buffer (no per-tile D2H, no host paste)."""
         if not self.tile_mode:
-            return self.compute_optical_flow(frames, frame_idx)
+            return self.compute_optical_flow(frames, frame_idx, return_device=return_device)
         if not self.core.is_model_loaded():
             raise RuntimeError("Model not loaded. Call load_model() first.")
         height, width = frames[frame_idx].shape[:2]
@@ -142,6 +147,8 @@ class VideoFlowProcessor:
                 tile_pbar.update(4)
             if overall_pbar is not None:
                 overall_pbar.update(1)
+        if return_device:
+            return full.permute(1, 2, 0)
         return full.permute(1, 2, 0).cpu().numpy()
 
     # ------------------------------------------------------------------ misc API
