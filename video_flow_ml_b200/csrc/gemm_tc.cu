@@ -26,7 +26,10 @@
 namespace vfml {
 
 constexpr int TC_BM = 128, TC_BK = 64;
-constexpr int TC_EPI_WARPS = 8;
+#ifndef VFML_TC_EPI_WARPS
+#define VFML_TC_EPI_WARPS 8
+#endif
+constexpr int TC_EPI_WARPS = VFML_TC_EPI_WARPS;      // multiple of 4: warp w may only read TMEM lanes 32 (w % 4) ..
 constexpr int TC_THREADS = 64 + TC_EPI_WARPS * 32;
 constexpr int TC_MAX_STAGES = 8;
 constexpr int TC_VEC_MAX = 2048;      // columns of bias / dw vectors staged in shared memory
@@ -83,6 +86,24 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64
         "setp.ne.b32 p, %4, 0;\n"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
         "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+}
+// one lane of a converged warp (the same lane every time for a full mask).  The producer and MMA warps run their loops with
+// all 32 lanes and predicate only the issue on this: addresses, descriptors and ring counters then stay warp-uniform, the
+// compiler keeps them in uniform registers, and UTMALDG / UTCHMMA / UTCBAR take them directly.  Under `if (lane == 0)` the
+// same values count as divergent and every such instruction is wrapped in an ELECT / R2UR.BROADCAST / BRA.U.ANY
+// uniformisation loop: ~100 cycles of single-thread issue latency per MMA, more than a 128 x 176 x 16 MMA executes in.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n.reg .pred P;\nelect.sync _|P, 0xFFFFFFFF;\nselp.b32 %0, 1, 0, P;\n}\n" : "=r"(pred));
+    return pred != 0;
+}
+__device__ __forceinline__ void st_global_256(void* ptr, const uint4& a, const uint4& b) {
+    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 ::"l"(ptr), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w) : "memory");
+}
+__device__ __forceinline__ void ld_global_256(const void* ptr, uint4& a, uint4& b) {
+    asm volatile("ld.global.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w) : "l"(ptr));
 }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -199,68 +220,102 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 
     // Everything above (barriers, TMEM, bias / dw vectors) and the resident weight tile below depend on constants only;
     // activations written by the preceding kernels are touched after griddepcontrol.wait.
-    if (warp == 0 && lane == 0 && p.b_res && p.b_is_const && t_first < t_end) {
+    if (warp == 0 && p.b_res && p.b_is_const && t_first < t_end && elect_one()) {
         mbar_expect_tx(&b_full, (uint32_t)nkb * b_bytes);
         for (int kb = 0; kb < nkb; ++kb) tma_load_3d(&mapB, &b_full, sB + (size_t)kb * b_stride, kb * TC_BK, n_fixed, 0);
     }
     asm volatile("griddepcontrol.wait;" ::: "memory");
 
     if (warp == 0) {
-        if (lane == 0) {
-            uint32_t it = 0;
-            long long t_wait = 0, t0 = clock64();
-            if (p.b_res && !p.b_is_const && t_first < t_end) {
-                mbar_expect_tx(&b_full, (uint32_t)nkb * b_bytes);
-                for (int kb = 0; kb < nkb; ++kb) tma_load_3d(&mapB, &b_full, sB + (size_t)kb * b_stride, kb * TC_BK, n_fixed, 0);
-            }
-            for (int tile = t_first; tile < t_end; tile += t_step) {
-                int bz, m0, n0;
-                tile_coords(tile, bz, m0, n0);
-                for (int kb = 0; kb < nkb; ++kb, ++it) {
-                    const int s = it % stages;
-                    const uint32_t ph = (it / stages) & 1u;
-                    const long long w0 = clock64();
-                    mbar_wait(&empty_bar[s], ph ^ 1u);
-                    t_wait += clock64() - w0;
-                    mbar_expect_tx(&full_bar[s], p.b_res ? a_bytes : a_bytes + b_bytes);
+        // ring position kept incrementally: an integer division by the runtime stage count on this issue path costs
+        // more than the k-block it feeds (scripts/micro/mma_loop.cu)
+        int s = 0;
+        uint32_t ph = 0;
+        const bool tr = p.trace != nullptr;
+        long long t_wait = 0, t0 = tr ? clock64() : 0;
+        if (p.b_res && !p.b_is_const && t_first < t_end && elect_one()) {
+            mbar_expect_tx(&b_full, (uint32_t)nkb * b_bytes);
+            for (int kb = 0; kb < nkb; ++kb) tma_load_3d(&mapB, &b_full, sB + (size_t)kb * b_stride, kb * TC_BK, n_fixed, 0);
+        }
+        __syncwarp();
+        const uint32_t tx_bytes = p.b_res ? a_bytes : a_bytes + b_bytes;
+        for (int tile = t_first; tile < t_end; tile += t_step) {
+            int bz, m0, n0;
+            tile_coords(tile, bz, m0, n0);
+            for (int kb = 0; kb < nkb; ++kb) {
+                const long long w0 = tr ? clock64() : 0;
+                mbar_wait(&empty_bar[s], ph ^ 1u);
+                if (tr) t_wait += clock64() - w0;
+                if (elect_one()) {
+#ifdef VFML_EXP_NOTMA
+                    mbar_arrive(&full_bar[s]);
+#else
+                    mbar_expect_tx(&full_bar[s], tx_bytes);
                     tma_load_3d(&mapA, &full_bar[s], sA + (size_t)s * a_bytes, kb * TC_BK, m0, bz);
                     if (!p.b_res) tma_load_3d(&mapB, &full_bar[s], sB + (size_t)s * b_stride, kb * TC_BK, n0, bz);
+#endif
                 }
+                __syncwarp();
+                if (++s == stages) { s = 0; ph ^= 1u; }
             }
-            if (p.trace) { p.trace[blockIdx.x * 8 + 0] = t_wait; p.trace[blockIdx.x * 8 + 1] = clock64() - t0; }
         }
+        if (tr && lane == 0) { p.trace[blockIdx.x * 8 + 0] = t_wait; p.trace[blockIdx.x * 8 + 1] = clock64() - t0; }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // instruction descriptor: D fp32, A/B fp16, both K-major, N = BN, M = 128
-            const uint32_t idesc = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
-            uint32_t it = 0, tl = 0;
-            long long t_we = 0, t_wf = 0, t0 = clock64();
-            if (p.b_res && t_first < t_end) mbar_wait(&b_full, 0);
-            for (int tile = t_first; tile < t_end; tile += t_step, ++tl) {
-                const uint32_t buf = tl & 1u, aph = (tl >> 1) & 1u;
-                const long long w0 = clock64();
-                mbar_wait(&acc_empty[buf], aph ^ 1u);          // epilogue has drained this accumulator
-                t_we += clock64() - w0;
+        // instruction descriptor: D fp32, A/B fp16, both K-major, N = BN, M = 128
+        const uint32_t idesc = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+        const bool tr = p.trace != nullptr;
+        long long t_we = 0, t_wf = 0, t0 = tr ? clock64() : 0;
+        if (p.b_res && t_first < t_end) mbar_wait(&b_full, 0);
+        // ring position, accumulator buffer and the operand descriptors are kept incrementally (no division, no
+        // descriptor rebuild per k-block): the descriptor's low 14 bits are the smem address >> 4, so stepping a
+        // stage is one 64-bit add
+        int s = 0;
+        uint32_t ph = 0, buf = 0, aph = 0;
+        const uint64_t adesc0 = make_sw128_desc(smem_u32(sA)), bdesc0 = make_sw128_desc(smem_u32(sB));
+        const uint64_t a_step = (uint64_t)(a_bytes >> 4), b_step = (uint64_t)(b_stride >> 4);
+        uint64_t adesc = adesc0, bdesc_s = bdesc0;
+        for (int tile = t_first; tile < t_end; tile += t_step) {
+            const long long w0 = tr ? clock64() : 0;
+            mbar_wait(&acc_empty[buf], aph ^ 1u);          // epilogue has drained this accumulator
+            if (tr) t_we += clock64() - w0;
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t tmem_d = tmem_base + buf * 256u;
+            uint64_t bdesc_k = bdesc0;
+            for (int kb = 0; kb < nkb; ++kb) {
+                const long long w1 = tr ? clock64() : 0;
+                mbar_wait(&full_bar[s], ph);
+                if (tr) t_wf += clock64() - w1;
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t tmem_d = tmem_base + buf * 256u;
-                for (int kb = 0; kb < nkb; ++kb, ++it) {
-                    const int s = it % stages;
-                    const uint32_t ph = (it / stages) & 1u;
-                    const long long w1 = clock64();
-                    mbar_wait(&full_bar[s], ph);
-                    t_wf += clock64() - w1;
-                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const uint64_t adesc = make_sw128_desc(smem_u32(sA + (size_t)s * a_bytes));
-                    const uint64_t bdesc = make_sw128_desc(smem_u32(sB + (size_t)(p.b_res ? kb : s) * b_stride));
+                const uint64_t bdesc = p.b_res ? bdesc_k : bdesc_s;
+                if (elect_one()) {
+#ifdef VFML_EXP_NOMMA
+                    if (p.alpha == 12345.0f) umma_f16(tmem_d, adesc, bdesc, idesc, 0u);
+                    mbar_arrive(&empty_bar[s]);
+#else
+                    umma_f16(tmem_d, adesc, bdesc, idesc, kb ? 1u : 0u);
 #pragma unroll
-                    for (int k = 0; k < TC_BK / 16; ++k)   // +32 bytes per K=16 step inside the 128-byte swizzle atom
-                        umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) ? 1u : 0u);
+                    for (int k = 1; k < TC_BK / 16; ++k)   // +32 bytes per K=16 step inside the 128-byte swizzle atom
+                        umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, 1u);
                     umma_commit(&empty_bar[s]);
+#endif
                 }
-                umma_commit(&acc_full[buf]);
+                __syncwarp();
+                bdesc_k += b_step;
+                adesc += a_step; bdesc_s += b_step;
+                if (++s == stages) { s = 0; ph ^= 1u; adesc = adesc0; bdesc_s = bdesc0; }
             }
-            if (p.trace) { p.trace[blockIdx.x * 8 + 2] = t_we; p.trace[blockIdx.x * 8 + 3] = t_wf; p.trace[blockIdx.x * 8 + 4] = clock64() - t0; }
+            if (elect_one()) {
+#ifdef VFML_EXP_NOMMA
+                mbar_arrive(&acc_full[buf]);
+#else
+                umma_commit(&acc_full[buf]);
+#endif
+            }
+            __syncwarp();
+            buf ^= 1u;
+            aph ^= buf ^ 1u;       // flips each time buf wraps back to 0
         }
+        if (tr && lane == 0) { p.trace[blockIdx.x * 8 + 2] = t_we; p.trace[blockIdx.x * 8 + 3] = t_wf; p.trace[blockIdx.x * 8 + 4] = clock64() - t0; }
     } else {
         long long e_wait = 0, e_t0 = clock64();
         const int q = warp & 3;                   // TMEM lane quarter this warp may access
@@ -286,6 +341,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             // software pipeline over this warp's 16-column chunks: the TMEM load and the residual load of
             // chunk i+1 are in flight while chunk i goes through the epilogue math and is stored
             const bool res_vec = has_res && row_ok && ((reinterpret_cast<uintptr_t>(rrow) & 15) == 0) && ((n0 & 7) == 0);
+            const bool res_256 = res_vec && ((reinterpret_cast<uintptr_t>(rrow + n0) & 31) == 0);   // chunks start at multiples of 16 columns
             const uint32_t trow = tmem_base + buf * 256u + ((uint32_t)(q * 32) << 16);
             uint32_t tc[16], tn[16];
             uint4 rc0 = make_uint4(0, 0, 0, 0), rc1 = rc0, rn0 = rc0, rn1 = rc0;
@@ -293,12 +349,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             const int cols_here = min(BN, p.N - n0);                       // valid columns of this tile
             const int share = ((cols_here + 15) / 16 + NCS - 1) / NCS * 16;   // columns per warp share, multiple of 16
             int c = hsel * share;
+#ifdef VFML_EXP_NOEPI
+            const int c_end = p.alpha == 12345.0f ? min(c + share, BN) : 0;
+#else
             const int c_end = min(c + share, BN);
+#endif
             if (c < c_end && n0 + c < p.N) {
                 tmem_ld16_issue(trow + (uint32_t)c, tc);
                 if (res_vec && n0 + c + 16 <= p.N) {
-                    rc0 = *reinterpret_cast<const uint4*>(rrow + n0 + c);
-                    rc1 = *reinterpret_cast<const uint4*>(rrow + n0 + c + 8);
+                    if (res_256) ld_global_256(rrow + n0 + c, rc0, rc1);
+                    else {
+                        rc0 = *reinterpret_cast<const uint4*>(rrow + n0 + c);
+                        rc1 = *reinterpret_cast<const uint4*>(rrow + n0 + c + 8);
+                    }
                 }
                 tmem_ld_wait(tc);
             }
@@ -310,8 +373,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 if (has_next) {
                     tmem_ld16_issue(trow + (uint32_t)cn, tn);
                     if (res_vec && n0 + cn + 16 <= p.N) {
-                        rn0 = *reinterpret_cast<const uint4*>(rrow + n0 + cn);
-                        rn1 = *reinterpret_cast<const uint4*>(rrow + n0 + cn + 8);
+                        if (res_256) ld_global_256(rrow + n0 + cn, rn0, rn1);
+                        else {
+                            rn0 = *reinterpret_cast<const uint4*>(rrow + n0 + cn);
+                            rn1 = *reinterpret_cast<const uint4*>(rrow + n0 + cn + 8);
+                        }
                     }
                 }
                 if (row_ok) {
@@ -373,6 +439,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                             x[i] = gelu_fast2(add2(x[i], fma2(w2, x[i], b2)));
                         }
                     }
+#ifdef VFML_EXP_NOSTORE
+                    if (p.alpha == 12345.0f)
+#endif
                     if (p.out_f32) {
                         if (full && ((reinterpret_cast<uintptr_t>(d32 + n) & 15) == 0)) {
 #pragma unroll
@@ -395,8 +464,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                                 h0[i] = __float22half2_rn(x[i]);
                                 h1[i] = __float22half2_rn(x[4 + i]);
                             }
-                            *reinterpret_cast<uint4*>(d16 + n) = o0;
-                            *reinterpret_cast<uint4*>(d16 + n + 8) = o1;
+                            // a row's 16 columns are one 32-byte sector when aligned: one 256-bit store = one whole-sector
+                            // write request to L2 instead of two half-sector ones (the epilogue's limiter: each lane of a
+                            // store instruction addresses a different row, so every request is a separate L2 transaction)
+                            if ((reinterpret_cast<uintptr_t>(d16 + n) & 31) == 0) st_global_256(d16 + n, o0, o1);
+                            else {
+                                *reinterpret_cast<uint4*>(d16 + n) = o0;
+                                *reinterpret_cast<uint4*>(d16 + n + 8) = o1;
+                            }
                         } else {
 #pragma unroll
                             for (int i = 0; i < 8; ++i) {
