@@ -5,7 +5,7 @@ import torch
 from video_flow_ml_b200 import ops
 mode = sys.argv[1] if len(sys.argv) > 1 else "plain"
 dev = "cuda"
-def buf(n, c): return torch.randn((n, (c + 7) // 8 * 8), device=dev).half()[:, :c]
+def buf(n, c): return torch.randn((n, (c + 15) // 16 * 16), device=dev).half()[:, :c]
 M, N, K = 42240, 486, 324
 x, w, o, r = buf(M, K), buf(N, K), buf(M, N), buf(M, N)
 b = torch.randn(N, device=dev)

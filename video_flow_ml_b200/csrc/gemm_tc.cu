@@ -27,7 +27,7 @@ namespace vfml {
 
 constexpr int TC_BM = 128, TC_BK = 64;
 #ifndef VFML_TC_EPI_WARPS
-#define VFML_TC_EPI_WARPS 8
+#define VFML_TC_EPI_WARPS 12
 #endif
 constexpr int TC_EPI_WARPS = VFML_TC_EPI_WARPS;      // multiple of 4: warp w may only read TMEM lanes 32 (w % 4) ..
 constexpr int TC_THREADS = 64 + TC_EPI_WARPS * 32;
@@ -147,6 +147,11 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
     return d;
 }
 
+// SPEC >= 0: the epilogue flag set (a subset of BIAS | RES | GELU | DW1) is a compile-time constant, the output is fp16,
+// alpha == 1 and the per-column vectors are in shared memory: the per-chunk epilogue becomes one basic block (no uniform
+// branches or constant-bank reloads between its stages), which the 3 epilogue warps per scheduler need to hide their
+// fixed-latency dependency stalls.  SPEC < 0: everything decided at run time.
+template <int SPEC>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const TcParams p) {
     // programmatic dependent launch: the next kernel of the stream may start its prologue as soon as every CTA of this
@@ -321,8 +326,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         const int q = warp & 3;                   // TMEM lane quarter this warp may access
         const int hsel = (warp - 2) >> 2;         // which CONTIGUOUS share of the tile's columns (contiguous: a thread's
                                                   // consecutive 32-byte stores complete whole 128-byte lines of its row)
-        const bool has_bias = p.epi & VFML_EPI_BIAS, has_res = p.epi & VFML_EPI_RES, has_dw = p.epi & VFML_EPI_DW1;
-        const bool do_gelu = p.epi & VFML_EPI_GELU, do_relu = p.epi & VFML_EPI_RELU;
+        constexpr bool SP = SPEC >= 0;
+        const uint32_t epi = SP ? (uint32_t)SPEC : p.epi;
+        const bool has_bias = epi & VFML_EPI_BIAS, has_res = epi & VFML_EPI_RES, has_dw = epi & VFML_EPI_DW1;
+        const bool do_gelu = epi & VFML_EPI_GELU, do_relu = epi & VFML_EPI_RELU;
+        const bool out_f32 = SP ? false : (bool)p.out_f32, vec_smem = SP ? true : (bool)p.vec_in_smem;
         const float2 alpha2 = splat(p.alpha);
         uint32_t tl = 0;
         for (int tile = t_first; tile < t_end; tile += t_step, ++tl) {
@@ -384,9 +392,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     const bool full = n + 16 <= p.N;
                     float2 x[8];
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) x[i] = mul2(make_float2(__uint_as_float(tc[2 * i]), __uint_as_float(tc[2 * i + 1])), alpha2);
+                    for (int i = 0; i < 8; ++i) {
+                        x[i] = make_float2(__uint_as_float(tc[2 * i]), __uint_as_float(tc[2 * i + 1]));
+                        if (!SP) x[i] = mul2(x[i], alpha2);
+                    }
                     if (has_bias) {
-                        if (p.vec_in_smem) {
+                        if (vec_smem) {
                             const float4* b4 = reinterpret_cast<const float4*>(s_vec + n);
 #pragma unroll
                             for (int i = 0; i < 4; ++i) {
@@ -428,7 +439,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
                             float2 w2, b2;
-                            if (p.vec_in_smem) {
+                            if (vec_smem) {
                                 w2 = *reinterpret_cast<const float2*>(s_vec + vec_cols + n + 2 * i);
                                 b2 = *reinterpret_cast<const float2*>(s_vec + 2 * vec_cols + n + 2 * i);
                             } else {
@@ -442,7 +453,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 #ifdef VFML_EXP_NOSTORE
                     if (p.alpha == 12345.0f)
 #endif
-                    if (p.out_f32) {
+                    if (out_f32) {
                         if (full && ((reinterpret_cast<uintptr_t>(d32 + n) & 15) == 0)) {
 #pragma unroll
                             for (int i = 0; i < 4; ++i)
@@ -555,13 +566,23 @@ static int pick_bn(int N) {
     return ((N + tiles - 1) / tiles + 15) / 16 * 16;
 }
 
+// kernel instances: [0] generic, the rest specialised on the epilogue flag set
+struct TcKernel { int spec; const void* fn; };
+#define TC_K(S) {S, reinterpret_cast<const void*>(&gemm_tc_kernel<S>)}
+static const TcKernel tc_kernels[] = {
+    TC_K(-1), TC_K(0), TC_K(VFML_EPI_BIAS), TC_K(VFML_EPI_BIAS | VFML_EPI_GELU), TC_K(VFML_EPI_BIAS | VFML_EPI_RES),
+    TC_K(VFML_EPI_BIAS | VFML_EPI_RES | VFML_EPI_GELU), TC_K(VFML_EPI_BIAS | VFML_EPI_RES | VFML_EPI_GELU | VFML_EPI_DW1)};
+#undef TC_K
+constexpr int TC_NUM_KERNELS = sizeof(tc_kernels) / sizeof(tc_kernels[0]);
+
 int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st) {
     static int num_sms = 0;
     if (!num_sms) {
         int dev = 0;
         VFML_CUDA(cudaGetDevice(&dev));
         VFML_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
-        VFML_CUDA(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 512));
+        for (int i = 0; i < TC_NUM_KERNELS; ++i)
+            VFML_CUDA(cudaFuncSetAttribute(tc_kernels[i].fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 512));
     }
     const size_t SMEM_MAX = 227 * 1024 - 512;
     const size_t a_bytes = TC_BM * TC_BK * 2;
@@ -641,7 +662,13 @@ int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = no_pdl ? 0 : 1;
-    cudaError_t le = cudaLaunchKernelEx(&cfg, gemm_tc_kernel, mapA, mapB, p);
+    const void* fn = tc_kernels[0].fn;
+    static const bool no_spec = getenv("VFML_GEMM_NO_SPEC") != nullptr;
+    if (!no_spec && !p.out_f32 && d.alpha == 1.0f && (!needs_vec || p.vec_in_smem))
+        for (int i = 1; i < TC_NUM_KERNELS; ++i)
+            if ((d.epi & ~VFML_EPI_WEIGHTS) == (uint32_t)tc_kernels[i].spec) fn = tc_kernels[i].fn;
+    void* args[3] = {&mapA, &mapB, &p};
+    cudaError_t le = cudaLaunchKernelExC(&cfg, fn, args);
     if (le != cudaSuccess) {
         set_error("gemm_tc: launch failed: %s", cudaGetErrorString(le));
         cudaGetLastError();

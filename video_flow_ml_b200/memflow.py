@@ -24,7 +24,7 @@ import torch
 from . import _lib
 from . import ops as _ops
 from .basic_encoder import BasicEncoder
-from .mof import MOFEngine, _PCWeights, _pad8, _pad_k
+from .mof import MOFEngine, _PCWeights, _pad8, _pad_act, _pad_k
 
 ITERS = 15                                      # configs/sintel_memflownet.py:24 (val_decoder_depth)
 TRAIN_AVG_LENGTH = (368 * 768 // 64) * 3 / 2    # configs/sintel_memflownet.py:28
@@ -129,8 +129,8 @@ class MemFlowEngine(MOFEngine):
                 "q": self._rows_buf(P, 128),
                 "keys": self._rows_buf(Tmax, 128),             # [current | stored frames]
                 "vT": torch.zeros((128, _pad8(Tmax)), dtype=self.dt, device=self.dev),
-                "attn": torch.zeros((P, _pad8(Tmax)), dtype=self.dt, device=self.dev),
-                "logits": torch.empty((P, _pad8(Tmax)), dtype=torch.float32, device=self.dev),
+                "attn": torch.zeros((P, _pad_act(Tmax)), dtype=self.dt, device=self.dev),
+                "logits": torch.empty((P, _pad_act(Tmax)), dtype=torch.float32, device=self.dev),
                 "delta": self._rows_buf(P, 4, torch.float32),  # [delta x, delta y, 0, 0]
                 "sa": self._rows_buf(P, 512),
                 "sb": self._rows_buf(P, 512),

@@ -32,6 +32,12 @@ def _pad8(c):
     return (c + 7) // 8 * 8
 
 
+def _pad_act(c):
+    """Row pitch of activation buffers: a multiple of 16 elements, so that every row of an fp16 buffer starts on a 32-byte
+    sector and the GEMM epilogue's 16-column pieces are single 256-bit stores (gemm_tc.cu)."""
+    return (c + 15) // 16 * 16
+
+
 def _pad_k(w):
     """[N, K] weight as a rows view whose pitch is a multiple of 8 elements (16-byte rows: TMA requirement)."""
     n, k = w.shape
@@ -120,7 +126,7 @@ class MOFEngine:
 
     # ------------------------------------------------------------------ buffers
     def _rows_buf(self, n, c, dtype=None):
-        pitch = _pad8(c)
+        pitch = _pad_act(c)
         return torch.zeros((n, pitch), dtype=dtype or self.dt, device=self.dev)[:, :c]
 
     def _workspace(self, Fc, h, w):
@@ -151,10 +157,10 @@ class MOFEngine:
 
     @staticmethod
     def _view(buf, n, c):
-        """[n, c] rows view carved from the start of a scratch buffer, pitch = pad8(c)."""
+        """[n, c] rows view carved from the start of a scratch buffer, pitch = _pad_act(c)."""
         base = buf._base if buf._base is not None else buf
         flat = base.reshape(-1)
-        pitch = _pad8(c)
+        pitch = _pad_act(c)
         if n * pitch > flat.numel():
             raise RuntimeError("scratch buffer too small")
         return flat[: n * pitch].view(n, pitch)[:, :c]
