@@ -118,3 +118,22 @@ def test_memflow_memory_policy_variants(max_f, min_f, every):
         assert (gu - wu).abs().max() < 2e-3, (t, (gu - wu).abs().max())
         stored = 0 if want.mem_k is None else want.mem_k.shape[-1] // P
         assert eng.n_stored == stored, (t, eng.n_stored, stored)
+
+
+@pytest.mark.parametrize("T,H,W", [(7, 124, 188), (9, 124, 252)])
+def test_engine_dataflow_long_sequences(mof_weights, T, H, W):
+    """Sequence lengths 7 and 9 (BASELINE.json configs[4] and configs[2]; `set_sequence_length`,
+    videoflow_processor.py:191-195) on frame sizes that need padding (a pyramid level of height 1 makes the reference itself return NaN: bilinear_sampler divides by H-1, so 96-row inputs are avoided):
+    T-2 centre frames, 2(T-2) flows, the temporal hidden-state warp reaches across every neighbour pair."""
+    frames = cases.mof_case(seed=77, n_frames=T + 1, H=H, W=W)
+    win = omof.pad_frames(omof.frames_to_window(frames, T // 2, T)).contiguous()
+    assert win.shape[1] == T and win.shape[-2] % 8 == 0 and win.shape[-1] % 8 == 0
+    of, on, oi = omof.mof_encode(win, mof_weights)
+    want = omof.mof_refine(of, on, oi, mof_weights, iters=2)
+    eng = MOFEngine(mof_weights, "cpu", torch.float32, iters=2, ops=fake_ops)
+    got = eng.refine(of, on, oi)
+    assert got.shape == want.shape == (1, 2 * (T - 2), 2, win.shape[-2], win.shape[-1])
+    assert (got - want).abs().max() < 2e-3, (got - want).abs().max()
+    mid = (T - 2) // 2                               # the flow VideoFlowCore returns: centre frame -> next
+    sel = eng.refine(of, on, oi, select=mid)
+    assert (sel - want[0, mid]).abs().max() < 2e-3

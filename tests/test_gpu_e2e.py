@@ -234,3 +234,23 @@ def test_device_resident_post_pass(processor_g10):
         out_np = host_taa.apply_taa(enc_np, flow_np)
         out_dev = dev_taa.apply_taa(enc_dev, flow_dev, return_device=True)
         assert out_dev.is_cuda and np.array_equal(out_dev.cpu().numpy().astype(out_np.dtype), out_np)
+
+
+@pytest.mark.parametrize("T,H,W,precision,tol", [(7, 124, 188, "fp32", 1e-2), (9, 124, 252, "fp32", 1e-2),
+                                                 (7, 124, 188, "fp16", 5e-2)])
+def test_mof_long_sequences_match_oracle(T, H, W, precision, tol):
+    """Sequence lengths 7 and 9 (BASELINE.json configs[4] / configs[2]) through `set_sequence_length`
+    (videoflow_processor.py:191-195): window choice, T-2 centre frames, returned flow index T-2, against the pinned
+    oracle on the same frames and weights (well-conditioned weight set).  Tolerances: the north star's."""
+    from video_flow_ml_b200.processing import VideoFlowProcessor
+    sd = omof.mof_synthetic_weights(0, gain=1.0)
+    p = VideoFlowProcessor("cuda", sequence_length=5, precision=precision)
+    p.set_sequence_length(T)
+    p.core.load_state_dict(sd, iters=8)
+    frames = cases.mof_case(seed=77, n_frames=T + 1, H=H, W=W)
+    idx = T // 2
+    flow = p.compute_optical_flow(list(frames), idx)
+    assert flow.shape == (H, W, 2) and flow.dtype == np.float32
+    win = omof.frames_to_window(frames, idx, T)
+    want = omof.core_compute_flow(win, sd, iters=8).permute(1, 2, 0).numpy()     # flow index T-2 (SURVEY Q2)
+    assert epe(flow, want) <= tol, epe(flow, want)

@@ -17,6 +17,9 @@
 //   2. k x 32 MMAs per warp, accumulators (4 m-blocks x 4 n-blocks) in registers;
 //   3. epilogue in place: centre value + bias + accumulator -> polynomial GELU -> fp16 back into the plane;
 //   4. transpose-store: 8 planes -> 16-byte channel vectors, coalesced rows.
+#include <cuda.h>
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "gelu_poly.cuh"
 
@@ -76,10 +79,17 @@ __global__ void dwconv_pack_kernel(const float* __restrict__ wgt, __half* __rest
     }
 }
 
-template <int K>
+// TMA = true: the input window arrives through the tensor memory accelerator instead of per-thread 16-byte loads.  Those
+// loads touch one 128-byte line per thread (pixel pitch >= 256 B), i.e. one LSU data-stage wavefront per pixel, and the
+// ncu capture (profiles/r1_dwconv_tc_ncu_summary.txt) shows the LSU data pipe as the busiest unit of this kernel (60 % for
+// k = 7, with 26 points of it from global accesses).  One 4-D box {8 channels, 48 columns, rows, 1 image} per half window
+// lands pixel-major in the (not yet used) plane region, zero-filled outside the image and beyond channel C; the threads
+// then pull it into registers with 128-bit shared loads (1/8 wavefront per pixel) and scatter it into the planes as before.
+template <int K, bool TMA>
 __global__ void __launch_bounds__(256, 2)
-dwconv_tc_kernel(const __half* __restrict__ x, __half* __restrict__ y, int h, int w, int C, int64_t px, int64_t py,
-                 const __half* __restrict__ packed, const float* __restrict__ bias, int tiles_x, int tiles_y) {
+dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __half* __restrict__ x, __half* __restrict__ y, int h, int w,
+                 int C, int64_t px, int64_t py, const __half* __restrict__ packed, const float* __restrict__ bias, int tiles_x,
+                 int tiles_y) {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // lets a PDL-launched successor start its prologue
     using Cfg = DtCfg<K>;
     constexpr int R = Cfg::R, INH = Cfg::INH, PLANE = Cfg::PLANE, WCH = Cfg::WCH;
@@ -94,6 +104,22 @@ dwconv_tc_kernel(const __half* __restrict__ x, __half* __restrict__ y, int h, in
     const int grp = blockIdx.y, c0 = grp * DT_CG;
     const int n0 = tx_i * DT_TW, y0 = ty_i * DT_TH;
     const int64_t img_row0 = (int64_t)img * h * w;
+    __shared__ uint64_t tma_bar;
+    if (TMA) {
+        if (tid == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&tma_bar)));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            constexpr int HALF = (INH + 1) / 2;                 // two boxes of HALF rows (the second may overhang the
+            const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&tma_bar);      // window: rows the kernel never reads)
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(2u * HALF * DT_INW * 16u) : "memory");
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+                asm volatile(
+                    "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+                    ::"r"(s_planes + b * HALF * DT_INW * 16), "l"(&mapX), "r"(bar), "r"(c0), "r"(n0 - 8), "r"(y0 - R + b * HALF), "r"(img)
+                    : "memory");
+        }
+    }
 
     // ---- 1a. band table of this channel group: K*16 uint4 per channel, asynchronous (lands while 1b runs)
     {
@@ -108,17 +134,30 @@ dwconv_tc_kernel(const __half* __restrict__ x, __half* __restrict__ y, int h, in
     {
         constexpr int NPIX = INH * DT_INW;
         constexpr int CH = (NPIX + 255) / 256;             // every load of the thread in flight at once
+        if (TMA) {
+            const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&tma_bar);
+            asm volatile(
+                "{\n.reg .pred p;\nDW_WAIT:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n@p bra DW_DONE;\nbra DW_WAIT;\nDW_DONE:\n}\n"
+                ::"r"(bar) : "memory");
+        }
         for (int p0 = 0; p0 < NPIX; p0 += 256 * CH) {
             uint4 v[CH];
 #pragma unroll
             for (int i = 0; i < CH; ++i) {
                 const int p = p0 + i * 256 + tid;
-                const int row = p / DT_INW, xi = p - row * DT_INW;
-                const int gy = y0 - R + row, gx = n0 - 8 + xi;
                 v[i] = make_uint4(0u, 0u, 0u, 0u);
-                if (p < NPIX && gy >= 0 && gy < h && gx >= 0 && gx < w)
-                    v[i] = __ldg(reinterpret_cast<const uint4*>(x + (img_row0 + (int64_t)gy * w + gx) * px + c0));
+                if (TMA) {
+                    if (p < NPIX)
+                        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];\n"
+                                     : "=r"(v[i].x), "=r"(v[i].y), "=r"(v[i].z), "=r"(v[i].w) : "r"(s_planes + p * 16));
+                } else {
+                    const int row = p / DT_INW, xi = p - row * DT_INW;
+                    const int gy = y0 - R + row, gx = n0 - 8 + xi;
+                    if (p < NPIX && gy >= 0 && gy < h && gx >= 0 && gx < w)
+                        v[i] = __ldg(reinterpret_cast<const uint4*>(x + (img_row0 + (int64_t)gy * w + gx) * px + c0));
+                }
             }
+            if (TMA) __syncthreads();          // the pixel-major window aliases the planes: everyone has read it
 #pragma unroll
             for (int i = 0; i < CH; ++i) {
                 const int p = p0 + i * 256 + tid;
@@ -223,18 +262,57 @@ dwconv_tc_kernel(const __half* __restrict__ x, __half* __restrict__ y, int h, in
     }
 }
 
+// 4-D map of a rows-layout activation [n_img][h][w][C] (pitch px halfs per pixel): box = {8 channels, 48 columns, rows, 1}
+static int make_window_map(CUtensorMap* map, const void* base, int n_img, int h, int w, int C, int64_t px, int box_rows) {
+    typedef CUresult (*encode_fn_t)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static encode_fn_t encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) {
+            set_error("dwconv_tc: cuTensorMapEncodeTiled is not available from the driver (%s)", cudaGetErrorString(e));
+            return VFML_ERR_CUDA;
+        }
+        encode = reinterpret_cast<encode_fn_t>(fn);
+    }
+    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n_img};
+    cuuint64_t strides[3] = {(cuuint64_t)px * 2, (cuuint64_t)px * 2 * w, (cuuint64_t)px * 2 * w * h};
+    cuuint32_t box[4] = {(cuuint32_t)DT_CG, (cuuint32_t)DT_INW, (cuuint32_t)box_rows, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("dwconv_tc: cuTensorMapEncodeTiled failed: CUresult %d (n=%d h=%d w=%d C=%d pitch=%lld)", (int)r, n_img, h, w, C,
+                  (long long)px);
+        return VFML_ERR_CUDA;
+    }
+    return VFML_OK;
+}
+
 template <int K>
 static int launch_dw_tc(const __half* x, __half* y, int n_img, int h, int w, int C, int64_t px, int64_t py,
                         const __half* packed, const float* bias, cudaStream_t st) {
-    auto kern = dwconv_tc_kernel<K>;
     static bool attr_done = false;
     if (!attr_done) {
-        VFML_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, DtCfg<K>::SMEM));
+        VFML_CUDA(cudaFuncSetAttribute(dwconv_tc_kernel<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DtCfg<K>::SMEM));
+        VFML_CUDA(cudaFuncSetAttribute(dwconv_tc_kernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DtCfg<K>::SMEM));
         attr_done = true;
     }
     const int tiles_x = cdiv(w, DT_TW), tiles_y = cdiv(h, DT_TH);
     dim3 grid(tiles_x * tiles_y * n_img, cdiv(C, DT_CG));
-    kern<<<grid, 256, DtCfg<K>::SMEM, st>>>(x, y, h, w, C, px, py, packed, bias, tiles_x, tiles_y);
+    static const bool no_tma = getenv("VFML_DW_TMA") == nullptr;      // opt-in until verified on the GPU
+    CUtensorMap mapX{};
+    if (!no_tma) {
+        const int rc = make_window_map(&mapX, x, n_img, h, w, C, px, (DtCfg<K>::INH + 1) / 2);
+        if (rc) return rc;
+        dwconv_tc_kernel<K, true><<<grid, 256, DtCfg<K>::SMEM, st>>>(mapX, x, y, h, w, C, px, py, packed, bias, tiles_x, tiles_y);
+    } else {
+        dwconv_tc_kernel<K, false><<<grid, 256, DtCfg<K>::SMEM, st>>>(mapX, x, y, h, w, C, px, py, packed, bias, tiles_x, tiles_y);
+    }
     VFML_LAUNCH_CHECK("dwconv_tc");
     return VFML_OK;
 }
