@@ -25,6 +25,9 @@
 
 namespace vfml {
 
+#ifndef VFML_DW_PAIRED
+#define VFML_DW_PAIRED 0      // opt-in (-DVFML_DW_PAIRED=1) until verified on the GPU
+#endif
 constexpr int DT_TH = 64, DT_TW = 32, DT_CG = 8;
 constexpr int DT_INW = 48;                 // input columns staged: x = n0 - 8 .. n0 + 39
 constexpr int DT_PITCH = 112;              // bytes per plane row (48 halfs + 8 pad)
@@ -42,6 +45,9 @@ template <int K> struct DtCfg {
 __device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
     asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];\n"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x2(uint32_t& r0, uint32_t& r1, uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x2.shared.b16 {%0,%1}, [%2];\n" : "=r"(r0), "=r"(r1) : "r"(addr));
 }
 __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
     asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
@@ -85,9 +91,11 @@ __global__ void dwconv_pack_kernel(const float* __restrict__ wgt, __half* __rest
 // k = 7, with 26 points of it from global accesses).  One 4-D box {8 channels, 48 columns, rows, 1 image} per half window
 // lands pixel-major in the (not yet used) plane region, zero-filled outside the image and beyond channel C; the threads
 // then pull it into registers with 128-bit shared loads (1/8 wavefront per pixel) and scatter it into the planes as before.
-template <int K, bool TMA>
+// TMA bit 1: the output tile leaves the same way (planes -> pixel-major chunks staged in the band-table region, which is
+// free after the MMA phase -> bulk tensor stores, clipped at the image border and at channel C by the unit).
+template <int K, int TMA>
 __global__ void __launch_bounds__(256, 2)
-dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __half* __restrict__ x, __half* __restrict__ y, int h, int w,
+dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapY, const __half* __restrict__ x, __half* __restrict__ y, int h, int w,
                  int C, int64_t px, int64_t py, const __half* __restrict__ packed, const float* __restrict__ bias, int tiles_x,
                  int tiles_y) {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // lets a PDL-launched successor start its prologue
@@ -105,7 +113,7 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __half* __restr
     const int n0 = tx_i * DT_TW, y0 = ty_i * DT_TH;
     const int64_t img_row0 = (int64_t)img * h * w;
     __shared__ uint64_t tma_bar;
-    if (TMA) {
+    if (TMA & 1) {
         if (tid == 0) {
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&tma_bar)));
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -134,7 +142,7 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __half* __restr
     {
         constexpr int NPIX = INH * DT_INW;
         constexpr int CH = (NPIX + 255) / 256;             // every load of the thread in flight at once
-        if (TMA) {
+        if (TMA & 1) {
             const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&tma_bar);
             asm volatile(
                 "{\n.reg .pred p;\nDW_WAIT:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n@p bra DW_DONE;\nbra DW_WAIT;\nDW_DONE:\n}\n"
@@ -146,7 +154,7 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __half* __restr
             for (int i = 0; i < CH; ++i) {
                 const int p = p0 + i * 256 + tid;
                 v[i] = make_uint4(0u, 0u, 0u, 0u);
-                if (TMA) {
+                if (TMA & 1) {
                     if (p < NPIX)
                         asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];\n"
                                      : "=r"(v[i].x), "=r"(v[i].y), "=r"(v[i].z), "=r"(v[i].w) : "r"(s_planes + p * 16));
@@ -157,7 +165,7 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __half* __restr
                         v[i] = __ldg(reinterpret_cast<const uint4*>(x + (img_row0 + (int64_t)gy * w + gx) * px + c0));
                 }
             }
-            if (TMA) __syncthreads();          // the pixel-major window aliases the planes: everyone has read it
+            if (TMA & 1) __syncthreads();          // the pixel-major window aliases the planes: everyone has read it
 #pragma unroll
             for (int i = 0; i < CH; ++i) {
                 const int p = p0 + i * 256 + tid;
@@ -178,20 +186,15 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __half* __restr
     // ---- 2. MMAs: warp <-> channel; 4 m-blocks (16 rows) x 4 n-blocks (8 columns)
     const uint32_t plane = s_planes + warp * PLANE;
     // ldmatrix.x4 lane address: matrices (rows 0-7 | 8-15) x (k 0-7 | 8-15)
-    const uint32_t a_lane = plane + ((lane & 7) + ((lane >> 3) & 1) * 8) * DT_PITCH + (lane >> 4) * 16;
+    [[maybe_unused]] const uint32_t a_lane = plane + ((lane & 7) + ((lane >> 3) & 1) * 8) * DT_PITCH + (lane >> 4) * 16;
     // B fragment words of the 4 band variants (delta = 16*kb - 8*s in {0, 16, -8, 8}): b0 = taps of rows
     // k = 2*(lane%4) + {0,1}, column n = lane/4; b1 = rows k + 8.  Tap index t = k - n + delta - 8 + R.
-    uint32_t w_lane[4][2];
-    {
-        const int deltas[4] = {0, 16, -8, 8};
-#pragma unroll
-        for (int d = 0; d < 4; ++d)
-#pragma unroll
-            for (int r = 0; r < 2; ++r) {
-                const int u0 = 2 * (lane & 3) + 8 * r - (lane >> 2) + deltas[d] - 8 + R + DT_WLEFT;
-                w_lane[d][r] = s_w + warp * WCH + ((u0 & 1) ? 128 : 0) + (u0 & ~1) * 2;
-            }
-    }
+    // All eight (variant, half) addresses differ from w_base by compile-time constants: 8 r + delta is even, so the parity
+    // (even / odd copy) is the lane's own and the rest is a byte offset of 2 (8 r + delta).
+    const int u_base = 2 * (lane & 3) - (lane >> 2) - 8 + R + DT_WLEFT;
+    const uint32_t w_base = s_w + warp * WCH + ((u_base & 1) ? 128 : 0) + (u_base & ~1) * 2;
+    constexpr int W_OFF[4][2] = {{0, 16}, {32, 48}, {-16, 0}, {16, 32}};       // 2 * (8 r + {0, 16, -8, 8}[d])
+#define w_lane(d, r) (w_base + W_OFF[d][r])
     float acc[4][4][4];
 #pragma unroll
     for (int mb = 0; mb < 4; ++mb)
@@ -200,13 +203,64 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __half* __restr
 #pragma unroll
             for (int i = 0; i < 4; ++i) acc[mb][s][i] = 0.0f;
 
+#if VFML_DW_PAIRED
+    // The A block of (mb, dy) is rows 16 mb + dy .. + 15 of the plane = two 8-row groups; the block of (mb, dy + 8) starts at
+    // the second of them.  Walking the row classes r = dy mod 8 and, per class, the groups at rows r + 8 j once each
+    // (one ldmatrix.x4 + one .x2 per group: 3 k-blocks x 2 halves), every group serves the two blocks it belongs to:
+    // 426 instead of 720 8x8 matrices per warp for k = 15 (k = 7 has no dy >= 8: same loads as before).  The shared-memory
+    // pipe is this kernel's busiest unit, and ldmatrix is most of its traffic in the MMA phase.
+    const uint32_t g_lane4 = plane + (lane & 7) * DT_PITCH + (lane >> 3) * 16;                 // k-blocks 0, 1 (lo | hi halves)
+    const uint32_t g_lane2 = plane + (lane & 7) * DT_PITCH + 64 + ((lane >> 3) & 1) * 16;      // k-block 2
+#pragma unroll
+    for (int r = 0; r < (K < 8 ? K : 8); ++r) {
+        const bool two = r + 8 < K;
+        uint32_t b[2][4][2];
+#pragma unroll
+        for (int d = 0; d < 4; ++d) {
+            b[0][d][0] = dt_lds32(w_lane(d, 0) + r * DT_WROW);
+            b[0][d][1] = dt_lds32(w_lane(d, 1) + r * DT_WROW);
+            if (two) {
+                b[1][d][0] = dt_lds32(w_lane(d, 0) + (r + 8) * DT_WROW);
+                b[1][d][1] = dt_lds32(w_lane(d, 1) + (r + 8) * DT_WROW);
+            } else {
+                b[1][d][0] = b[1][d][1] = 0u;
+            }
+        }
+        uint32_t gp[6] = {0u, 0u, 0u, 0u, 0u, 0u};
+#pragma unroll
+        for (int j = 0; j <= 8; ++j) {
+            if (!two && j == 8) break;
+            uint32_t gc[6];
+            {
+                uint32_t t4[4];
+                ldsm_x4(t4, g_lane4 + (r + 8 * j) * DT_PITCH);
+                gc[0] = t4[0]; gc[1] = t4[1]; gc[2] = t4[2]; gc[3] = t4[3];
+                ldsm_x2(gc[4], gc[5], g_lane2 + (r + 8 * j) * DT_PITCH);
+            }
+            if (j >= 1) {
+                const int jb = j - 1, mb = jb >> 1, hi = jb & 1;
+                if (hi == 0 || two) {
+                    const uint32_t a0[4] = {gp[0], gc[0], gp[1], gc[1]};
+                    const uint32_t a1[4] = {gp[2], gc[2], gp[3], gc[3]};
+                    const uint32_t a2[4] = {gp[4], gc[4], gp[5], gc[5]};
+                    mma16816(acc[mb][0], a0, b[hi][0][0], b[hi][0][1]); mma16816(acc[mb][0], a1, b[hi][1][0], b[hi][1][1]);
+                    mma16816(acc[mb][1], a0, b[hi][2][0], b[hi][2][1]); mma16816(acc[mb][1], a1, b[hi][3][0], b[hi][3][1]);
+                    mma16816(acc[mb][2], a1, b[hi][0][0], b[hi][0][1]); mma16816(acc[mb][2], a2, b[hi][1][0], b[hi][1][1]);
+                    mma16816(acc[mb][3], a1, b[hi][2][0], b[hi][2][1]); mma16816(acc[mb][3], a2, b[hi][3][0], b[hi][3][1]);
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 6; ++i) gp[i] = gc[i];
+        }
+    }
+#else
 #pragma unroll
     for (int dy = 0; dy < K; ++dy) {
         uint32_t b[4][2];
 #pragma unroll
         for (int d = 0; d < 4; ++d) {
-            b[d][0] = dt_lds32(w_lane[d][0] + dy * DT_WROW);
-            b[d][1] = dt_lds32(w_lane[d][1] + dy * DT_WROW);
+            b[d][0] = dt_lds32(w_lane(d, 0) + dy * DT_WROW);
+            b[d][1] = dt_lds32(w_lane(d, 1) + dy * DT_WROW);
         }
 #pragma unroll
         for (int mb = 0; mb < 4; ++mb) {
@@ -222,6 +276,8 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __half* __restr
             mma16816(acc[mb][3], a1, b[2][0], b[2][1]); mma16816(acc[mb][3], a2, b[3][0], b[3][1]);
         }
     }
+
+#endif
 
     // ---- 3. epilogue in place (this warp is the only user of its plane): gelu(x + conv + bias)
     {
@@ -247,6 +303,39 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __half* __restr
     __syncthreads();
 
     // ---- 4. transpose-store: 8 planes -> one 16-byte channel vector per pixel
+    if (TMA & 2) {
+        constexpr int CR = K == 15 ? 16 : 8;                 // rows per chunk: two chunk buffers fit in the band-table region
+        constexpr int CHUNK = CR * DT_TW * 16;
+        static_assert(2 * CHUNK <= DT_CG * WCH, "store staging does not fit in the band-table region");
+#pragma unroll 1
+        for (int c = 0; c < DT_TH / CR; ++c) {
+            if (y0 + c * CR >= h) break;
+            const uint32_t stage = s_w + (c & 1) * CHUNK;
+            if (c >= 2) {                                    // the store issued two chunks ago has read this buffer
+                if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                __syncthreads();
+            }
+            for (int p = tid; p < CR * DT_TW; p += 256) {
+                const int row = c * CR + (p >> 5), col = p & 31;
+                const uint32_t a = s_planes + (row + R) * DT_PITCH + (col + 8) * 2;
+                uint4 v;
+                v.x = dt_lds16(a + 0 * PLANE) | (dt_lds16(a + 1 * PLANE) << 16);
+                v.y = dt_lds16(a + 2 * PLANE) | (dt_lds16(a + 3 * PLANE) << 16);
+                v.z = dt_lds16(a + 4 * PLANE) | (dt_lds16(a + 5 * PLANE) << 16);
+                v.w = dt_lds16(a + 6 * PLANE) | (dt_lds16(a + 7 * PLANE) << 16);
+                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};\n" ::"r"(stage + p * 16), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncthreads();
+            if (tid == 0) {
+                asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+                             ::"l"(&mapY), "r"(stage), "r"(c0), "r"(n0), "r"(y0 + c * CR), "r"(img) : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+        }
+        if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        return;
+    }
     for (int p = tid; p < DT_TH * DT_TW; p += 256) {
         const int row = p >> 5, col = p & 31;
         const int gy = y0 + row, gx = n0 + col;
@@ -263,7 +352,8 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __half* __restr
 }
 
 // 4-D map of a rows-layout activation [n_img][h][w][C] (pitch px halfs per pixel): box = {8 channels, 48 columns, rows, 1}
-static int make_window_map(CUtensorMap* map, const void* base, int n_img, int h, int w, int C, int64_t px, int box_rows) {
+static int make_window_map(CUtensorMap* map, const void* base, int n_img, int h, int w, int C, int64_t px, int box_cols,
+                           int box_rows) {
     typedef CUresult (*encode_fn_t)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                     const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -280,7 +370,7 @@ static int make_window_map(CUtensorMap* map, const void* base, int n_img, int h,
     }
     cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n_img};
     cuuint64_t strides[3] = {(cuuint64_t)px * 2, (cuuint64_t)px * 2 * w, (cuuint64_t)px * 2 * w * h};
-    cuuint32_t box[4] = {(cuuint32_t)DT_CG, (cuuint32_t)DT_INW, (cuuint32_t)box_rows, 1};
+    cuuint32_t box[4] = {(cuuint32_t)DT_CG, (cuuint32_t)box_cols, (cuuint32_t)box_rows, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -296,23 +386,29 @@ static int make_window_map(CUtensorMap* map, const void* base, int n_img, int h,
 template <int K>
 static int launch_dw_tc(const __half* x, __half* y, int n_img, int h, int w, int C, int64_t px, int64_t py,
                         const __half* packed, const float* bias, cudaStream_t st) {
+    typedef void (*kern_t)(const CUtensorMap, const CUtensorMap, const __half*, __half*, int, int, int, int64_t, int64_t, const __half*,
+                           const float*, int, int);
+    static const kern_t kerns[4] = {dwconv_tc_kernel<K, 0>, dwconv_tc_kernel<K, 1>, dwconv_tc_kernel<K, 2>, dwconv_tc_kernel<K, 3>};
     static bool attr_done = false;
     if (!attr_done) {
-        VFML_CUDA(cudaFuncSetAttribute(dwconv_tc_kernel<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DtCfg<K>::SMEM));
-        VFML_CUDA(cudaFuncSetAttribute(dwconv_tc_kernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DtCfg<K>::SMEM));
+        for (int i = 0; i < 4; ++i)
+            VFML_CUDA(cudaFuncSetAttribute(kerns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, DtCfg<K>::SMEM));
         attr_done = true;
     }
     const int tiles_x = cdiv(w, DT_TW), tiles_y = cdiv(h, DT_TH);
     dim3 grid(tiles_x * tiles_y * n_img, cdiv(C, DT_CG));
-    static const bool no_tma = getenv("VFML_DW_TMA") == nullptr;      // opt-in until verified on the GPU
-    CUtensorMap mapX{};
-    if (!no_tma) {
-        const int rc = make_window_map(&mapX, x, n_img, h, w, C, px, (DtCfg<K>::INH + 1) / 2);
+    // VFML_DW_TMA: bit 0 = window load through TMA, bit 1 = tile store through TMA (opt-in until verified on the GPU)
+    static const int mode = getenv("VFML_DW_TMA") ? atoi(getenv("VFML_DW_TMA")) & 3 : 0;
+    CUtensorMap mapX{}, mapY{};
+    if (mode & 1) {
+        const int rc = make_window_map(&mapX, x, n_img, h, w, C, px, DT_INW, (DtCfg<K>::INH + 1) / 2);
         if (rc) return rc;
-        dwconv_tc_kernel<K, true><<<grid, 256, DtCfg<K>::SMEM, st>>>(mapX, x, y, h, w, C, px, py, packed, bias, tiles_x, tiles_y);
-    } else {
-        dwconv_tc_kernel<K, false><<<grid, 256, DtCfg<K>::SMEM, st>>>(mapX, x, y, h, w, C, px, py, packed, bias, tiles_x, tiles_y);
     }
+    if (mode & 2) {
+        const int rc = make_window_map(&mapY, y, n_img, h, w, C, py, DT_TW, K == 15 ? 16 : 8);
+        if (rc) return rc;
+    }
+    kerns[mode]<<<grid, 256, DtCfg<K>::SMEM, st>>>(mapX, mapY, x, y, h, w, C, px, py, packed, bias, tiles_x, tiles_y);
     VFML_LAUNCH_CHECK("dwconv_tc");
     return VFML_OK;
 }
