@@ -357,6 +357,41 @@ def test_tiled_lookup_matches_oracle(ops, n, h, w, math_f32):
     close(unperm.view(n, h, w, 324).permute(0, 3, 1, 2), want_o, 4.0 * 2.0 ** -11 * scale + 1e-6)
 
 
+def test_tiled_lookup_full_size_integer_coordinates(ops):
+    """BASELINE.json full size (436x1024 -> 55x128 features, one frame: a 99 MB level-0 volume).  Size-independent
+    properties of the lookup (core/corr.py:31-56): at coordinates that are multiples of 8 every level's window centre is
+    an integer, all bilinear weights are exactly 0 or 1, so (a) the tiled fp16 kernel, the rows kernel and a plain gather
+    agree BIT-EXACTLY, and (b) the 81 taps of a level sum to the 9x9 box sum of that level's zero-padded map
+    (a checksum that does not depend on the tap order)."""
+    import torch.nn.functional as F
+    n, h, w = 1, 55, 128
+    P = h * w
+    r = np.random.default_rng(123)
+    f1 = r.standard_normal((n, 64, h, w)).astype(np.float32)
+    f2 = r.standard_normal((n, 64, h, w)).astype(np.float32)
+    cx = torch.from_numpy(8 * r.integers(0, w // 8, size=(n, 1, h, w))).float()
+    cy = torch.from_numpy(8 * r.integers(0, (h + 7) // 8, size=(n, 1, h, w))).float()
+    coords = cu(torch.cat([cx, cy], 1))
+    pyr16 = ops.corr_volume_pyramid(cu(f1), cu(f2), 4, torch.float16)
+    tp = ops.corr_tile_pyramid(pyr16[0].view(P, P), h, w)
+    want = torch.zeros((P, 324), dtype=torch.float32, device="cuda")
+    ops.corr_lookup(pyr16, coords, 4, out=want)
+    perm = ops.corr_lookup_perm("cuda")
+    for math_f32 in (False, True):
+        got = rows_buf(P, 324, torch.float16, pad=4)
+        ops.corr_lookup_tiled(tp, None, coords, None, got, None, math_f32=math_f32)
+        unperm = torch.empty_like(want)
+        unperm[:, perm] = got.float()
+        assert torch.equal(unperm, want), (unperm - want).abs().max().item()
+    ix, iy = coords[0, 0].reshape(-1).long(), coords[0, 1].reshape(-1).long()
+    q = torch.arange(P, device="cuda")
+    for l, lev in enumerate(pyr16):
+        box = F.avg_pool2d(F.pad(lev.double(), (8, 8, 8, 8)), 9, stride=1, divisor_override=1)   # [P, 1, hl + 8, wl + 8]
+        s_want = box[q, 0, (iy >> l) + 4, (ix >> l) + 4]
+        s_got = unperm[:, 81 * l:81 * (l + 1)].double().sum(-1)
+        assert torch.allclose(s_got, s_want, rtol=0, atol=1e-9), (l, (s_got - s_want).abs().max().item())
+
+
 def test_tiled_volume_pair_launch(ops):
     """fmaps -> tiled pyramid in one call; both directions in one launch equal two single launches."""
     n, h, w = 2, 24, 40

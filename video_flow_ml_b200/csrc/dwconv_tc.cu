@@ -28,6 +28,9 @@ namespace vfml {
 #ifndef VFML_DW_PAIRED
 #define VFML_DW_PAIRED 0      // opt-in (-DVFML_DW_PAIRED=1) until verified on the GPU
 #endif
+#ifndef VFML_DW_K8
+#define VFML_DW_K8 0          // opt-in (-DVFML_DW_K8=1) until verified on the GPU
+#endif
 constexpr int DT_TH = 64, DT_TW = 32, DT_CG = 8;
 constexpr int DT_INW = 48;                 // input columns staged: x = n0 - 8 .. n0 + 39
 constexpr int DT_PITCH = 112;              // bytes per plane row (48 halfs + 8 pad)
@@ -53,6 +56,10 @@ __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], 
     asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
                  : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void mma1688(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};\n"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3]) : "r"(a0), "r"(a1), "r"(b0));
 }
 __device__ __forceinline__ uint32_t dt_lds32(uint32_t a) {
     uint32_t v;
@@ -243,10 +250,18 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant
                     const uint32_t a0[4] = {gp[0], gc[0], gp[1], gc[1]};
                     const uint32_t a1[4] = {gp[2], gc[2], gp[3], gc[3]};
                     const uint32_t a2[4] = {gp[4], gc[4], gp[5], gc[5]};
+#if VFML_DW_K8
+                    // an 8-column output block reads 8 + 2R <= 22 inputs = three 8-column chunks: one k16 + one k8 MMA
+                    mma16816(acc[mb][0], a0, b[hi][0][0], b[hi][0][1]); mma1688(acc[mb][0], gp[2], gc[2], b[hi][1][0]);
+                    mma1688(acc[mb][1], gp[1], gc[1], b[hi][2][1]);     mma16816(acc[mb][1], a1, b[hi][3][0], b[hi][3][1]);
+                    mma16816(acc[mb][2], a1, b[hi][0][0], b[hi][0][1]); mma1688(acc[mb][2], gp[4], gc[4], b[hi][1][0]);
+                    mma1688(acc[mb][3], gp[3], gc[3], b[hi][2][1]);     mma16816(acc[mb][3], a2, b[hi][3][0], b[hi][3][1]);
+#else
                     mma16816(acc[mb][0], a0, b[hi][0][0], b[hi][0][1]); mma16816(acc[mb][0], a1, b[hi][1][0], b[hi][1][1]);
                     mma16816(acc[mb][1], a0, b[hi][2][0], b[hi][2][1]); mma16816(acc[mb][1], a1, b[hi][3][0], b[hi][3][1]);
                     mma16816(acc[mb][2], a1, b[hi][0][0], b[hi][0][1]); mma16816(acc[mb][2], a2, b[hi][1][0], b[hi][1][1]);
                     mma16816(acc[mb][3], a1, b[hi][2][0], b[hi][2][1]); mma16816(acc[mb][3], a2, b[hi][3][0], b[hi][3][1]);
+#endif
                 }
             }
 #pragma unroll
@@ -270,10 +285,21 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant
             ldsm_x4(a1, ar + 32);
             ldsm_x4(a2, ar + 64);
             // n-block s uses k-blocks (s/2, s/2 + 1) with variants (0,1) for even s and (2,3) for odd s
+#if VFML_DW_K8
+            // An 8-column output block reads 8 + 2R <= 22 inputs, which lie in three 8-column chunks of the plane: one k16
+            // MMA on the aligned chunk pair and one k8 MMA on the third chunk (the other half of that k-block only ever
+            // met zero band entries): 12 instead of 16 k8-equivalents per row block on the legacy tensor pipe, which the
+            // ncu capture puts at ~10 cycles per m16n8k16 and sub-partition, i.e. half of this kernel's run time.
+            mma16816(acc[mb][0], a0, b[0][0], b[0][1]); mma1688(acc[mb][0], a1[0], a1[1], b[1][0]);
+            mma1688(acc[mb][1], a0[2], a0[3], b[2][1]); mma16816(acc[mb][1], a1, b[3][0], b[3][1]);
+            mma16816(acc[mb][2], a1, b[0][0], b[0][1]); mma1688(acc[mb][2], a2[0], a2[1], b[1][0]);
+            mma1688(acc[mb][3], a1[2], a1[3], b[2][1]); mma16816(acc[mb][3], a2, b[3][0], b[3][1]);
+#else
             mma16816(acc[mb][0], a0, b[0][0], b[0][1]); mma16816(acc[mb][0], a1, b[1][0], b[1][1]);
             mma16816(acc[mb][1], a0, b[2][0], b[2][1]); mma16816(acc[mb][1], a1, b[3][0], b[3][1]);
             mma16816(acc[mb][2], a1, b[0][0], b[0][1]); mma16816(acc[mb][2], a2, b[1][0], b[1][1]);
             mma16816(acc[mb][3], a1, b[2][0], b[2][1]); mma16816(acc[mb][3], a2, b[3][0], b[3][1]);
+#endif
         }
     }
 

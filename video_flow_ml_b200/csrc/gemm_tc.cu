@@ -611,6 +611,24 @@ int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st) {
             }
             break;
         }
+        // (3) wave quantisation (experiment, VFML_GEMM_WAVE=<c0>): each CTA walks ceil(m_tiles / (SMs / nt)) row tiles of its
+        // column tile; 165 row tiles on 148 SMs cost two rounds with nt = 1 but three half-width rounds with nt = 2.
+        // Cost model: rounds x (c0 + BN) column-equivalents, c0 = fixed cost of a tile (fill, drain, barrier hand-offs).
+        static const int wave_c0 = getenv("VFML_GEMM_WAVE") ? atoi(getenv("VFML_GEMM_WAVE")) : 0;
+        if (wave_c0 > 0) {
+            auto cost = [&](int nt, int bn) {
+                const int rounds = b_res ? cdiv(m_tiles, std::max(1, num_sms / nt)) : cdiv((int64_t)m_tiles * nt, num_sms);
+                return (double)rounds * (wave_c0 + bn);
+            };
+            double best = cost(n_tiles, BN);
+            const int nt0 = n_tiles;
+            for (int nt = nt0 + 1; nt <= nt0 + 3; ++nt) {
+                const int bn = ((d.N + nt - 1) / nt + 15) / 16 * 16;
+                if (bn < 48 || (nt - 1) * bn >= d.N) continue;
+                const double c = cost(nt, bn);
+                if (c < 0.95 * best) { best = c; BN = bn; n_tiles = nt; }
+            }
+        }
     }
     CUtensorMap mapA, mapB;
     int rc = make_map(&mapA, d.A, d.K, d.M, d.batch, d.lda, d.strideA, TC_BM);
