@@ -1,13 +1,15 @@
 #!/bin/bash
 # depthwise kernel variants side by side (run under gpurun).  Variant libraries (prebuilt, scripts/micro/libvfml_<v>.so):
-#   u = baseline MMA loop, p = paired-dy ldmatrix sharing, *_k8 = k16 + k8 MMA split; VFML_DW_TMA: bit 0 TMA load, bit 1 TMA store
+#   u = baseline MMA loop, u_k8 = k16 + k8 MMA split; VFML_DW_TMA: bit 0 TMA load, bit 1 TMA store; VFML_DW_TH: tile rows
 mkdir -p gpurun_out
 cp video_flow_ml_b200/libvfml.so /tmp/libvfml_orig.so
-for v in u p u_k8 p_k8; do
+for v in u u_k8; do
   cp scripts/micro/libvfml_$v.so video_flow_ml_b200/libvfml.so
+  for th in 64 32; do
   for m in 0 3; do
-    echo "== variant $v VFML_DW_TMA=$m: tests"; VFML_DW_TMA=$m timeout 200 python -m pytest tests/test_gpu_ops.py -m gpu -x -q -k dwconv 2>&1 | tail -2
+    echo "== variant $v TH=$th VFML_DW_TMA=$m: tests"; VFML_DW_TH=$th VFML_DW_TMA=$m timeout 200 python -m pytest tests/test_gpu_ops.py -m gpu -x -q -k dwconv 2>&1 | tail -2
   done
-  for m in 0 1 2 3; do echo "== variant $v VFML_DW_TMA=$m: timing"; VFML_DW_TMA=$m timeout 100 python scripts/micro/dw_only.py; done
+  for m in 0 1 2 3; do echo "== variant $v TH=$th VFML_DW_TMA=$m: timing"; VFML_DW_TH=$th VFML_DW_TMA=$m timeout 100 python scripts/micro/dw_only.py 2>&1 | tail -5; done
+  done
 done
 cp /tmp/libvfml_orig.so video_flow_ml_b200/libvfml.so

@@ -25,21 +25,18 @@
 
 namespace vfml {
 
-#ifndef VFML_DW_PAIRED
-#define VFML_DW_PAIRED 0      // opt-in (-DVFML_DW_PAIRED=1) until verified on the GPU
-#endif
 #ifndef VFML_DW_K8
 #define VFML_DW_K8 0          // opt-in (-DVFML_DW_K8=1) until verified on the GPU
 #endif
-constexpr int DT_TH = 64, DT_TW = 32, DT_CG = 8;
+constexpr int DT_TW = 32, DT_CG = 8;        // tile height TH (64 or 32 rows) is a template parameter
 constexpr int DT_INW = 48;                 // input columns staged: x = n0 - 8 .. n0 + 39
 constexpr int DT_PITCH = 112;              // bytes per plane row (48 halfs + 8 pad)
 constexpr int DT_WROW = 256;               // bytes per (channel, dy) band row: even copy [64 halfs] + odd copy [64 halfs]
 constexpr int DT_WLEFT = 24;               // tap t lives at index t + 24 of the even copy
 
-template <int K> struct DtCfg {
+template <int K, int TH> struct DtCfg {
     static constexpr int R = K / 2;
-    static constexpr int INH = DT_TH + K - 1;
+    static constexpr int INH = TH + K - 1;
     static constexpr int PLANE = INH * DT_PITCH;
     static constexpr int WCH = K * DT_WROW + 16;          // +16 B: channels land in different banks
     static constexpr int SMEM = DT_CG * PLANE + DT_CG * WCH;
@@ -48,9 +45,6 @@ template <int K> struct DtCfg {
 __device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
     asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];\n"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
-}
-__device__ __forceinline__ void ldsm_x2(uint32_t& r0, uint32_t& r1, uint32_t addr) {
-    asm volatile("ldmatrix.sync.aligned.m8n8.x2.shared.b16 {%0,%1}, [%2];\n" : "=r"(r0), "=r"(r1) : "r"(addr));
 }
 __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
     asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
@@ -100,13 +94,17 @@ __global__ void dwconv_pack_kernel(const float* __restrict__ wgt, __half* __rest
 // then pull it into registers with 128-bit shared loads (1/8 wavefront per pixel) and scatter it into the planes as before.
 // TMA bit 1: the output tile leaves the same way (planes -> pixel-major chunks staged in the band-table region, which is
 // free after the MMA phase -> bulk tensor stores, clipped at the image border and at channel C by the unit).
-template <int K, int TMA>
-__global__ void __launch_bounds__(256, 2)
+// TH = 64: 2 CTAs per SM (100 KB, 128 registers).  TH = 32: 3 CTAs per SM (72 KB, 85 registers) and twice the CTAs: the
+// grid of the benchmark shapes (600 / 768 / 984 CTAs on 296 slots) loses up to a third of its run time to the last
+// partial wave, and a CTA's phases (load, MMA, epilogue, store) only overlap with those of its SM neighbours.
+template <int K, int TMA, int TH>
+__global__ void __launch_bounds__(256, TH == 64 ? 2 : 3)
 dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapY, const __half* __restrict__ x, __half* __restrict__ y, int h, int w,
                  int C, int64_t px, int64_t py, const __half* __restrict__ packed, const float* __restrict__ bias, int tiles_x,
                  int tiles_y) {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // lets a PDL-launched successor start its prologue
-    using Cfg = DtCfg<K>;
+    using Cfg = DtCfg<K, TH>;
+    constexpr int MB = TH / 16;                       // 16-row MMA blocks per tile
     constexpr int R = Cfg::R, INH = Cfg::INH, PLANE = Cfg::PLANE, WCH = Cfg::WCH;
     extern __shared__ __align__(128) uint8_t dt_smem[];
     const uint32_t s_planes = (uint32_t)__cvta_generic_to_shared(dt_smem);
@@ -117,13 +115,16 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant
     const int ty_i = (tile_id / tiles_x) % tiles_y;
     const int img = tile_id / (tiles_x * tiles_y);
     const int grp = blockIdx.y, c0 = grp * DT_CG;
-    const int n0 = tx_i * DT_TW, y0 = ty_i * DT_TH;
+    const int n0 = tx_i * DT_TW, y0 = ty_i * TH;
     const int64_t img_row0 = (int64_t)img * h * w;
     __shared__ uint64_t tma_bar;
     if (TMA & 1) {
         if (tid == 0) {
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&tma_bar)));
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();            // nobody may poll the barrier before it is initialised (the word holds a previous kernel's data)
+        if (tid == 0) {
             constexpr int HALF = (INH + 1) / 2;                 // two boxes of HALF rows (the second may overhang the
             const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&tma_bar);      // window: rows the kernel never reads)
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(2u * HALF * DT_INW * 16u) : "memory");
@@ -193,7 +194,7 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant
     // ---- 2. MMAs: warp <-> channel; 4 m-blocks (16 rows) x 4 n-blocks (8 columns)
     const uint32_t plane = s_planes + warp * PLANE;
     // ldmatrix.x4 lane address: matrices (rows 0-7 | 8-15) x (k 0-7 | 8-15)
-    [[maybe_unused]] const uint32_t a_lane = plane + ((lane & 7) + ((lane >> 3) & 1) * 8) * DT_PITCH + (lane >> 4) * 16;
+    const uint32_t a_lane = plane + ((lane & 7) + ((lane >> 3) & 1) * 8) * DT_PITCH + (lane >> 4) * 16;
     // B fragment words of the 4 band variants (delta = 16*kb - 8*s in {0, 16, -8, 8}): b0 = taps of rows
     // k = 2*(lane%4) + {0,1}, column n = lane/4; b1 = rows k + 8.  Tap index t = k - n + delta - 8 + R.
     // All eight (variant, half) addresses differ from w_base by compile-time constants: 8 r + delta is even, so the parity
@@ -202,73 +203,14 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant
     const uint32_t w_base = s_w + warp * WCH + ((u_base & 1) ? 128 : 0) + (u_base & ~1) * 2;
     constexpr int W_OFF[4][2] = {{0, 16}, {32, 48}, {-16, 0}, {16, 32}};       // 2 * (8 r + {0, 16, -8, 8}[d])
 #define w_lane(d, r) (w_base + W_OFF[d][r])
-    float acc[4][4][4];
+    float acc[MB][4][4];
 #pragma unroll
-    for (int mb = 0; mb < 4; ++mb)
+    for (int mb = 0; mb < MB; ++mb)
 #pragma unroll
         for (int s = 0; s < 4; ++s)
 #pragma unroll
             for (int i = 0; i < 4; ++i) acc[mb][s][i] = 0.0f;
 
-#if VFML_DW_PAIRED
-    // The A block of (mb, dy) is rows 16 mb + dy .. + 15 of the plane = two 8-row groups; the block of (mb, dy + 8) starts at
-    // the second of them.  Walking the row classes r = dy mod 8 and, per class, the groups at rows r + 8 j once each
-    // (one ldmatrix.x4 + one .x2 per group: 3 k-blocks x 2 halves), every group serves the two blocks it belongs to:
-    // 426 instead of 720 8x8 matrices per warp for k = 15 (k = 7 has no dy >= 8: same loads as before).  The shared-memory
-    // pipe is this kernel's busiest unit, and ldmatrix is most of its traffic in the MMA phase.
-    const uint32_t g_lane4 = plane + (lane & 7) * DT_PITCH + (lane >> 3) * 16;                 // k-blocks 0, 1 (lo | hi halves)
-    const uint32_t g_lane2 = plane + (lane & 7) * DT_PITCH + 64 + ((lane >> 3) & 1) * 16;      // k-block 2
-#pragma unroll
-    for (int r = 0; r < (K < 8 ? K : 8); ++r) {
-        const bool two = r + 8 < K;
-        uint32_t b[2][4][2];
-#pragma unroll
-        for (int d = 0; d < 4; ++d) {
-            b[0][d][0] = dt_lds32(w_lane(d, 0) + r * DT_WROW);
-            b[0][d][1] = dt_lds32(w_lane(d, 1) + r * DT_WROW);
-            if (two) {
-                b[1][d][0] = dt_lds32(w_lane(d, 0) + (r + 8) * DT_WROW);
-                b[1][d][1] = dt_lds32(w_lane(d, 1) + (r + 8) * DT_WROW);
-            } else {
-                b[1][d][0] = b[1][d][1] = 0u;
-            }
-        }
-        uint32_t gp[6] = {0u, 0u, 0u, 0u, 0u, 0u};
-#pragma unroll
-        for (int j = 0; j <= 8; ++j) {
-            if (!two && j == 8) break;
-            uint32_t gc[6];
-            {
-                uint32_t t4[4];
-                ldsm_x4(t4, g_lane4 + (r + 8 * j) * DT_PITCH);
-                gc[0] = t4[0]; gc[1] = t4[1]; gc[2] = t4[2]; gc[3] = t4[3];
-                ldsm_x2(gc[4], gc[5], g_lane2 + (r + 8 * j) * DT_PITCH);
-            }
-            if (j >= 1) {
-                const int jb = j - 1, mb = jb >> 1, hi = jb & 1;
-                if (hi == 0 || two) {
-                    const uint32_t a0[4] = {gp[0], gc[0], gp[1], gc[1]};
-                    const uint32_t a1[4] = {gp[2], gc[2], gp[3], gc[3]};
-                    const uint32_t a2[4] = {gp[4], gc[4], gp[5], gc[5]};
-#if VFML_DW_K8
-                    // an 8-column output block reads 8 + 2R <= 22 inputs = three 8-column chunks: one k16 + one k8 MMA
-                    mma16816(acc[mb][0], a0, b[hi][0][0], b[hi][0][1]); mma1688(acc[mb][0], gp[2], gc[2], b[hi][1][0]);
-                    mma1688(acc[mb][1], gp[1], gc[1], b[hi][2][1]);     mma16816(acc[mb][1], a1, b[hi][3][0], b[hi][3][1]);
-                    mma16816(acc[mb][2], a1, b[hi][0][0], b[hi][0][1]); mma1688(acc[mb][2], gp[4], gc[4], b[hi][1][0]);
-                    mma1688(acc[mb][3], gp[3], gc[3], b[hi][2][1]);     mma16816(acc[mb][3], a2, b[hi][3][0], b[hi][3][1]);
-#else
-                    mma16816(acc[mb][0], a0, b[hi][0][0], b[hi][0][1]); mma16816(acc[mb][0], a1, b[hi][1][0], b[hi][1][1]);
-                    mma16816(acc[mb][1], a0, b[hi][2][0], b[hi][2][1]); mma16816(acc[mb][1], a1, b[hi][3][0], b[hi][3][1]);
-                    mma16816(acc[mb][2], a1, b[hi][0][0], b[hi][0][1]); mma16816(acc[mb][2], a2, b[hi][1][0], b[hi][1][1]);
-                    mma16816(acc[mb][3], a1, b[hi][2][0], b[hi][2][1]); mma16816(acc[mb][3], a2, b[hi][3][0], b[hi][3][1]);
-#endif
-                }
-            }
-#pragma unroll
-            for (int i = 0; i < 6; ++i) gp[i] = gc[i];
-        }
-    }
-#else
 #pragma unroll
     for (int dy = 0; dy < K; ++dy) {
         uint32_t b[4][2];
@@ -278,7 +220,7 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant
             b[d][1] = dt_lds32(w_lane(d, 1) + dy * DT_WROW);
         }
 #pragma unroll
-        for (int mb = 0; mb < 4; ++mb) {
+        for (int mb = 0; mb < MB; ++mb) {
             uint32_t a0[4], a1[4], a2[4];
             const uint32_t ar = a_lane + (mb * 16 + dy) * DT_PITCH;
             ldsm_x4(a0, ar);
@@ -303,14 +245,13 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant
         }
     }
 
-#endif
 
     // ---- 3. epilogue in place (this warp is the only user of its plane): gelu(x + conv + bias)
     {
         const int c = c0 + warp;
         const float bv = c < C ? __ldg(bias + c) : 0.0f;
 #pragma unroll
-        for (int mb = 0; mb < 4; ++mb)
+        for (int mb = 0; mb < MB; ++mb)
 #pragma unroll
             for (int s = 0; s < 4; ++s)
 #pragma unroll
@@ -334,7 +275,7 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant
         constexpr int CHUNK = CR * DT_TW * 16;
         static_assert(2 * CHUNK <= DT_CG * WCH, "store staging does not fit in the band-table region");
 #pragma unroll 1
-        for (int c = 0; c < DT_TH / CR; ++c) {
+        for (int c = 0; c < TH / CR; ++c) {
             if (y0 + c * CR >= h) break;
             const uint32_t stage = s_w + (c & 1) * CHUNK;
             if (c >= 2) {                                    // the store issued two chunks ago has read this buffer
@@ -362,7 +303,7 @@ dwconv_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant
         if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         return;
     }
-    for (int p = tid; p < DT_TH * DT_TW; p += 256) {
+    for (int p = tid; p < TH * DT_TW; p += 256) {
         const int row = p >> 5, col = p & 31;
         const int gy = y0 + row, gx = n0 + col;
         if (gy < h && gx < w) {
@@ -409,34 +350,58 @@ static int make_window_map(CUtensorMap* map, const void* base, int n_img, int h,
     return VFML_OK;
 }
 
-template <int K>
+template <int K, int TH>
 static int launch_dw_tc(const __half* x, __half* y, int n_img, int h, int w, int C, int64_t px, int64_t py,
-                        const __half* packed, const float* bias, cudaStream_t st) {
+                        const __half* packed, const float* bias, int mode, cudaStream_t st) {
     typedef void (*kern_t)(const CUtensorMap, const CUtensorMap, const __half*, __half*, int, int, int, int64_t, int64_t, const __half*,
                            const float*, int, int);
-    static const kern_t kerns[4] = {dwconv_tc_kernel<K, 0>, dwconv_tc_kernel<K, 1>, dwconv_tc_kernel<K, 2>, dwconv_tc_kernel<K, 3>};
+    static const kern_t kerns[4] = {dwconv_tc_kernel<K, 0, TH>, dwconv_tc_kernel<K, 1, TH>, dwconv_tc_kernel<K, 2, TH>,
+                                    dwconv_tc_kernel<K, 3, TH>};
+    using Cfg = DtCfg<K, TH>;
     static bool attr_done = false;
     if (!attr_done) {
         for (int i = 0; i < 4; ++i)
-            VFML_CUDA(cudaFuncSetAttribute(kerns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, DtCfg<K>::SMEM));
+            VFML_CUDA(cudaFuncSetAttribute(kerns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
         attr_done = true;
     }
-    const int tiles_x = cdiv(w, DT_TW), tiles_y = cdiv(h, DT_TH);
+    const int tiles_x = cdiv(w, DT_TW), tiles_y = cdiv(h, TH);
     dim3 grid(tiles_x * tiles_y * n_img, cdiv(C, DT_CG));
-    // VFML_DW_TMA: bit 0 = window load through TMA, bit 1 = tile store through TMA (opt-in until verified on the GPU)
-    static const int mode = getenv("VFML_DW_TMA") ? atoi(getenv("VFML_DW_TMA")) & 3 : 0;
     CUtensorMap mapX{}, mapY{};
     if (mode & 1) {
-        const int rc = make_window_map(&mapX, x, n_img, h, w, C, px, DT_INW, (DtCfg<K>::INH + 1) / 2);
+        const int rc = make_window_map(&mapX, x, n_img, h, w, C, px, DT_INW, (Cfg::INH + 1) / 2);
         if (rc) return rc;
     }
     if (mode & 2) {
         const int rc = make_window_map(&mapY, y, n_img, h, w, C, py, DT_TW, K == 15 ? 16 : 8);
         if (rc) return rc;
     }
-    kerns[mode]<<<grid, 256, DtCfg<K>::SMEM, st>>>(mapX, mapY, x, y, h, w, C, px, py, packed, bias, tiles_x, tiles_y);
+    kerns[mode]<<<grid, 256, Cfg::SMEM, st>>>(mapX, mapY, x, y, h, w, C, px, py, packed, bias, tiles_x, tiles_y);
     VFML_LAUNCH_CHECK("dwconv_tc");
     return VFML_OK;
+}
+
+// Tile height: VFML_DW_TH=32|64 forces it; otherwise (VFML_DW_TH=0: auto) the one with the cheaper last wave under the model
+// "rounds x CTA cost", a 32-row CTA costing 0.56 of a 64-row one (half the MMAs, 46 instead of 78 window rows for k = 15).
+template <int K>
+static int launch_dw_tc_any(const __half* x, __half* y, int n_img, int h, int w, int C, int64_t px, int64_t py,
+                            const __half* packed, const float* bias, cudaStream_t st) {
+    // VFML_DW_TMA: bit 0 = window load through TMA, bit 1 = tile store through TMA (opt-in until verified on the GPU)
+    static const int mode = getenv("VFML_DW_TMA") ? atoi(getenv("VFML_DW_TMA")) & 3 : 0;
+    static const int th_env = getenv("VFML_DW_TH") ? atoi(getenv("VFML_DW_TH")) : 64;
+    static int num_sms = 0;
+    if (!num_sms) {
+        int dev = 0;
+        VFML_CUDA(cudaGetDevice(&dev));
+        VFML_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+    }
+    int th = th_env;
+    if (th != 32 && th != 64) {
+        const int64_t per = (int64_t)cdiv(w, DT_TW) * n_img * cdiv(C, DT_CG);
+        const double c64 = (double)cdiv(per * cdiv(h, 64), 2 * num_sms), c32 = 0.56 * cdiv(per * cdiv(h, 32), 3 * num_sms);
+        th = c32 < c64 ? 32 : 64;
+    }
+    return th == 32 ? launch_dw_tc<K, 32>(x, y, n_img, h, w, C, px, py, packed, bias, mode, st)
+                    : launch_dw_tc<K, 64>(x, y, n_img, h, w, C, px, py, packed, bias, mode, st);
 }
 
 }  // namespace vfml
@@ -476,6 +441,6 @@ extern "C" int vfml_dwconv_tc_res_gelu(const void* x, void* y, int n_img, int h,
     const __half* xi = reinterpret_cast<const __half*>(x);
     __half* yo = reinterpret_cast<__half*>(y);
     const __half* pk = reinterpret_cast<const __half*>(packed);
-    return k == 15 ? launch_dw_tc<15>(xi, yo, n_img, h, w, C, pitch_x, pitch_y, pk, bias, to_stream(s))
-                   : launch_dw_tc<7>(xi, yo, n_img, h, w, C, pitch_x, pitch_y, pk, bias, to_stream(s));
+    return k == 15 ? launch_dw_tc_any<15>(xi, yo, n_img, h, w, C, pitch_x, pitch_y, pk, bias, to_stream(s))
+                   : launch_dw_tc_any<7>(xi, yo, n_img, h, w, C, pitch_x, pitch_y, pk, bias, to_stream(s));
 }
