@@ -26,7 +26,7 @@
 namespace vfml {
 
 #ifndef VFML_DW_K8
-#define VFML_DW_K8 0          // opt-in (-DVFML_DW_K8=1) until verified on the GPU
+#define VFML_DW_K8 1          // k16 + k8 MMA split (measured -2 %); -DVFML_DW_K8=0 restores two k16 MMAs per block
 #endif
 constexpr int DT_TW = 32, DT_CG = 8;        // tile height TH (64 or 32 rows) is a template parameter
 constexpr int DT_INW = 48;                 // input columns staged: x = n0 - 8 .. n0 + 39
@@ -385,9 +385,11 @@ static int launch_dw_tc(const __half* x, __half* y, int n_img, int h, int w, int
 template <int K>
 static int launch_dw_tc_any(const __half* x, __half* y, int n_img, int h, int w, int C, int64_t px, int64_t py,
                             const __half* packed, const float* bias, cudaStream_t st) {
-    // VFML_DW_TMA: bit 0 = window load through TMA, bit 1 = tile store through TMA (opt-in until verified on the GPU)
-    static const int mode = getenv("VFML_DW_TMA") ? atoi(getenv("VFML_DW_TMA")) & 3 : 0;
-    static const int th_env = getenv("VFML_DW_TH") ? atoi(getenv("VFML_DW_TH")) : 64;
+    // VFML_DW_TMA: bit 0 = window load through TMA, bit 1 = tile store through TMA.  Default 3 and 32-row tiles: measured
+    // 181 -> 136 us over the four C1 depthwise shapes (scripts/micro/dw_ab.sh, profiles/r1_s18_dw_ab.txt); 0 / 64 = the
+    // previous configuration, kept for A/B.
+    static const int mode = getenv("VFML_DW_TMA") ? atoi(getenv("VFML_DW_TMA")) & 3 : 3;
+    static const int th_env = getenv("VFML_DW_TH") ? atoi(getenv("VFML_DW_TH")) : 32;
     static int num_sms = 0;
     if (!num_sms) {
         int dev = 0;
