@@ -611,10 +611,10 @@ int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st) {
             }
             break;
         }
-        // (3) wave quantisation (experiment, VFML_GEMM_WAVE=<c0>): each CTA walks ceil(m_tiles / (SMs / nt)) row tiles of its
+        // (3) wave quantisation (VFML_GEMM_WAVE=<c0>, default 32): each CTA walks ceil(m_tiles / (SMs / nt)) row tiles of its
         // column tile; 165 row tiles on 148 SMs cost two rounds with nt = 1 but three half-width rounds with nt = 2.
         // Cost model: rounds x (c0 + BN) column-equivalents, c0 = fixed cost of a tile (fill, drain, barrier hand-offs).
-        static const int wave_c0 = getenv("VFML_GEMM_WAVE") ? atoi(getenv("VFML_GEMM_WAVE")) : 0;
+        static const int wave_c0 = getenv("VFML_GEMM_WAVE") ? atoi(getenv("VFML_GEMM_WAVE")) : 32;   // measured: 29.68 -> 29.36 ms per window; 0 disables
         if (wave_c0 > 0) {
             auto cost = [&](int nt, int bn) {
                 const int rounds = b_res ? cdiv(m_tiles, std::max(1, num_sms / nt)) : cdiv((int64_t)m_tiles * nt, num_sms);
