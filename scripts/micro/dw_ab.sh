@@ -1,5 +1,7 @@
 #!/bin/bash
 # depthwise kernel variants side by side (run under gpurun).  Variant libraries (prebuilt, scripts/micro/libvfml_<v>.so):
+# build the variants first:  VFML_NVCC_EXTRA="-DVFML_DW_K8=0" VFML_LIB_OUT=scripts/micro/libvfml_u.so python -m video_flow_ml_b200.build
+#                             VFML_NVCC_EXTRA="-DVFML_DW_K8=1" VFML_LIB_OUT=scripts/micro/libvfml_u_k8.so python -m video_flow_ml_b200.build
 #   u = baseline MMA loop, u_k8 = k16 + k8 MMA split; VFML_DW_TMA: bit 0 TMA load, bit 1 TMA store; VFML_DW_TH: tile rows
 mkdir -p gpurun_out
 cp video_flow_ml_b200/libvfml.so /tmp/libvfml_orig.so
