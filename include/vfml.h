@@ -177,8 +177,41 @@ int vfml_decode_mv_rg8(const uint8_t* rgb, float* flow, int height, int width, f
                        vfml_stream_t s);
 
 /* ---------------------------------------------------------------------------------
+ * Remaining flow encoders / decoders, bit-exact with the reference's numpy / torchvision /
+ * OpenCV arithmetic given the same fp32 flow.  flow [h, w, 2] fp32, rgb [h, w, 3] u8.
+ *   vfml_encode_mv_rgb8   MotionVectorsRGB8FlowEncoder.encode, 'rgb+' method (encoding/flow_encoders.py:10,242-262,292-295)
+ *   vfml_decode_mv_rgb8   MotionVectorsRGB8FlowEncoder.decode, 'rgb+' (:308,340-347,362-369)
+ *   vfml_encode_hsv       HSVFlowEncoder.encode (:38-67) incl. cv2.cvtColor(HSV2RGB)
+ *   vfml_encode_torchvision  TorchvisionFlowEncoder.encode (:399-427): torchvision.utils.flow_to_image;
+ *                         ref_wrap = 1 also applies the reference's `(img * 255).astype(uint8)` on the uint8 image (:425)
+ * scratch4: 4 bytes of device memory (the max-magnitude reduction of the two normalising encoders).
+ * ------------------------------------------------------------------------------- */
+int vfml_encode_mv_rgb8(const float* flow, uint8_t* rgb, int height, int width, float clamp, vfml_stream_t s);
+int vfml_decode_mv_rgb8(const uint8_t* rgb, float* flow, int height, int width, float clamp, vfml_stream_t s);
+int vfml_encode_hsv(const float* flow, uint8_t* rgb, int height, int width, void* scratch4, vfml_stream_t s);
+int vfml_encode_torchvision(const float* flow, uint8_t* rgb, int height, int width, int ref_wrap, void* scratch4,
+                            vfml_stream_t s);
+
+/* ---------------------------------------------------------------------------------
+ * LOD pyramid of a flow field, LODGenerator.generate_lods (storage/cache_manager.py:77-161): level l+1 [ceil(h/2),
+ * ceil(w/2), 2] = 0.5 * mean over the existing cells of each 2x2 block of level l.  One launch writes num_levels
+ * (1..4) reduced levels into levels[0..num_levels-1] (HOST array of device pointers); chain calls for more.
+ * Bit-identical with the reference's per-pixel Python loop (same summation order).
+ * ------------------------------------------------------------------------------- */
+int vfml_lod_pyramid(const float* flow, int height, int width, float* const* levels, int num_levels, vfml_stream_t s);
+
+/* ---------------------------------------------------------------------------------
+ * Flow quality map, generate_quality_frame_gpu (correction_worker.py:175-208): frame1 / frame2 [h, w, 3] u8, flow
+ * [flow_h, flow_w, 2] fp32 (resized bilinearly, align_corners=False, and rescaled when its size differs, :182-185),
+ * out [h, w, 3] u8: green = similarity of frame1[p] and frame2[p - flow], red = dissimilar / out of bounds.
+ * ------------------------------------------------------------------------------- */
+int vfml_quality_frame(const uint8_t* frame1, const uint8_t* frame2, const float* flow, int flow_h, int flow_w,
+                       uint8_t* out, int height, int width, float threshold, vfml_stream_t s);
+
+/* ---------------------------------------------------------------------------------
  * Temporal anti-aliasing, effects/taa_processor.py:41-262.
- *   cur      : [h, w, 3] u8 current frame
+ *   cur      : [h, w, 3] current frame, u8 (cur_f32 = 0) or fp32 (cur_f32 = 1: the reference converts with
+ *              current_frame.astype(np.float32), :64, so float frames keep their fractions)
  *   flow     : [h, w, 2] fp32 (previous frame's flow, flow_processor.py:1018-1029) or NULL
  *   history  : [h, w, 3] f64 previous output; out: [h, w, 3] f64 (may not alias history)
  *   mode     : 0 = simple EMA (:78-80), 1 = flow + bilinear (:218-262), 2 = flow + bilateral (:149-216)
@@ -186,10 +219,10 @@ int vfml_decode_mv_rg8(const uint8_t* rgb, float* flow, int height, int width, f
  *              a sequence, and always in modes 0/1): colour weights / blends are then evaluated in
  *              fp32 exactly as numpy's dtype promotion does; values are still stored f64.
  * ------------------------------------------------------------------------------- */
-int vfml_taa(const uint8_t* cur, const float* flow, const double* history, double* out, int h, int w,
+int vfml_taa(const void* cur, int cur_f32, const float* flow, const double* history, double* out, int h, int w,
              double alpha, double sigma_color, int mode, int hist_f32, vfml_stream_t s);
 /* first frame of a sequence: out = double(cur) (taa_processor.py:70-74) */
-int vfml_taa_init(const uint8_t* cur, double* out, int h, int w, vfml_stream_t s);
+int vfml_taa_init(const void* cur, int cur_f32, double* out, int h, int w, vfml_stream_t s);
 
 /* ---------------------------------------------------------------------------------
  * Building blocks of the update step (MOFNetStack/stack.py, gma.py).

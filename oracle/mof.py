@@ -246,7 +246,16 @@ def mof_encode(images, sd, encoder=None):
     return fmaps, torch.tanh(net), torch.relu(inp)
 
 
-def mof_refine(fmaps, net, inp, sd, iters=ITERS, all_iters=False, trace=None):
+def _amp(dtype):
+    """Emulation of the reference's CUDA mixed-precision path (network.py:13,149,160,191: encoders, attention and
+    the update block under fp16 autocast; volume build and lookup in fp32, network.py:151 / corr.py:97) with
+    torch's CPU autocast.  Used only to measure the reference's OWN reduced-precision deviation (the noise floor
+    the fp16 tier is compared with, scripts/fp16_floor.py); dtype=None is the fp32 path."""
+    import contextlib
+    return torch.autocast("cpu", dtype=dtype) if dtype is not None else contextlib.nullcontext()
+
+
+def mof_refine(fmaps, net, inp, sd, iters=ITERS, all_iters=False, trace=None, amp=None):
     """Correlation build + ``iters`` update iterations + convex upsampling.
     fmaps [T,256,h,w] -> flows [1, 2(T-2), 2, 8h, 8w] (forward flows then backward flows).
     network.py:151-215 with B=1."""
@@ -255,7 +264,8 @@ def mof_refine(fmaps, net, inp, sd, iters=ITERS, all_iters=False, trace=None):
     h, w = fmaps.shape[-2:]
     fpyr = corr_pyramid(fmaps[1:T - 1], fmaps[2:T])
     bpyr = corr_pyramid(fmaps[1:T - 1], fmaps[0:T - 2])
-    attn = gma_attention(inp, sd)
+    with _amp(amp):
+        attn = gma_attention(inp, sd)
     c0 = pixel_grid(Fc, h, w)
     fc1, bc1 = c0.clone(), c0.clone()
     mhs = None
@@ -264,15 +274,16 @@ def mof_refine(fmaps, net, inp, sd, iters=ITERS, all_iters=False, trace=None):
         fcorr = corr_lookup(fpyr, fc1)
         bcorr = corr_lookup(bpyr, bc1)
         last = it == iters - 1
-        net, mhs, mask, delta = update_block(net, mhs, inp, fcorr, bcorr, fc1 - c0, bc1 - c0, c0, attn, 1, sd,
-                                             with_mask=(last or all_iters))
+        with _amp(amp):
+            net, mhs, mask, delta = update_block(net, mhs, inp, fcorr, bcorr, fc1 - c0, bc1 - c0, c0, attn, 1, sd,
+                                                 with_mask=(last or all_iters))
         fc1 = fc1 + delta[:, 0:2]
         bc1 = bc1 + delta[:, 2:4]
         if trace is not None:
             trace.append((fc1 - c0, bc1 - c0))
         if last or all_iters:
-            fu = convex_upsample8(fc1 - c0, mask[:, :576])
-            bu = convex_upsample8(bc1 - c0, mask[:, 576:])
+            fu = convex_upsample8((fc1 - c0).float(), mask[:, :576].float())
+            bu = convex_upsample8((bc1 - c0).float(), mask[:, 576:].float())
             outs.append(torch.cat([fu[None], bu[None]], 1))
     return outs if all_iters else outs[-1]
 
@@ -408,8 +419,15 @@ def synthetic_weights(shapes, seed=0, gain=None, overrides=None):
     return sd
 
 
-def mof_synthetic_weights(seed=0, gain=1.4, flow_gain=0.25):
+DRIFT = (0.6, 0.25, -0.5, -0.3)     # px per iteration at 1/8 resolution: fwd (x, y), bwd (x, y)
+
+
+def mof_synthetic_weights(seed=0, gain=1.4, flow_gain=0.25, drift=None):
     """Seeded synthetic MOFNet weights (checkpoints are absent: .MISSING_LARGE_BLOBS).
+    ``drift`` (4 floats, e.g. ``DRIFT``) is added to ``update_block.flow_head.ffn2.2.bias``: every iteration then
+    moves the forward / backward coordinates by about that many low-resolution texels, so over 32 iterations
+    the lookups travel ~19 texels (150 px), through the border and out of range, while the recurrence keeps the
+    conditioning of the gain it is combined with (the "large-motion" fixtures, tests/golden/make_golden_drift.py).
     Update-block weights get ``gain`` 1.4 so the recurrence is input-sensitive (low-res flow
     std ~2 px, |flow| up to ~12 px after 32 iterations on the float test clip: in-range, border and out-of-range
     taps all occur) without diverging; ``aggregator.gamma`` is 0.5 (it initialises to 0,
@@ -420,6 +438,8 @@ def mof_synthetic_weights(seed=0, gain=1.4, flow_gain=0.25):
         "update_block.flow_head.ffn2.2.weight": lambda t: t * flow_gain,
         "update_block.flow_head.ffn2.2.bias": lambda t: t * flow_gain,
     })
+    if drift is not None:
+        sd["update_block.flow_head.ffn2.2.bias"] = sd["update_block.flow_head.ffn2.2.bias"] + torch.tensor(drift, dtype=torch.float32)
     d = torch.arange(160).view(1, -1) - torch.arange(160).view(-1, 1)
     sd["att.pos_emb.rel_ind"] = d + 159            # gma.py:16-18 (buffer, unused in forward)
     return sd

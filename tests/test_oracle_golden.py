@@ -183,3 +183,100 @@ def test_memflow_oracle_matches_reference_golden(golden):
     flow = omem.core_compute_flow(mof.frames_to_window(frames, 2, 3), sd)
     assert flow.shape == (2, 124, 188)
     close(flow.numpy(), g["core_flow"], 2e-4)
+
+
+# ---------------------------------------------------------------------------- round 2 fixtures
+def _post2_inputs():
+    ff = cases.flow_field_case()
+    fin = np.nan_to_num(cases.flow_field_case(seed=31, h=45, w=61), nan=0.5, posinf=3.0, neginf=-3.0)
+    fe = np.nan_to_num(cases.flow_field_case(seed=37, h=64, w=96), nan=1.0, posinf=2.0, neginf=-2.0)
+    frames, flows = cases.taa_case(seed=41, n=3, h=33, w=47)
+    fl = flows[0] * 2
+    fl[3, 3] = [100.0, 0.0]
+    fl[4, 4] = [0.0, -100.0]
+    return ff, fin, fe, frames, fl
+
+
+def test_remaining_encoders_bit_exact(golden):
+    """rgb8 ('rgb+') encode / decode, HSV, torchvision: oracle == unmodified reference, bit for bit (post2.npz)."""
+    g = golden("post2.npz")
+    ff, fin, _, _, _ = _post2_inputs()
+    with np.errstate(all="ignore"):
+        assert np.array_equal(post.encode_mv_rgb8(ff), g["rgb8"])
+        assert np.array_equal(post.encode_mv_rgb8(ff, 8.0), g["rgb8_c8"])
+        assert np.array_equal(post.decode_mv_rgb8(g["rgb8"]), g["rgb8_decoded"])
+        assert np.array_equal(post.encode_mv_rgb8(ff, 64.0), g["mv_default"])          # encode_motion_vectors default = rgb8, clamp 64
+        assert np.array_equal(post.decode_mv_rgb8(g["mv_default"], 64.0), g["mv_default_decoded"])
+        assert np.array_equal(post.encode_hsv(ff), g["hsv"])
+        assert np.array_equal(post.encode_hsv(fin), g["hsv_fin"])
+        assert np.array_equal(post.encode_hsv(np.zeros((5, 7, 2), np.float32)), g["hsv_zero"])
+        assert np.array_equal(post.encode_torchvision(fin), g["tv"])
+
+
+def test_hsv2rgb_restatement_matches_opencv():
+    """The third-party step of the HSV encoder: exhaustive (H, S) at V = 255 and random V, SIMD body and scalar tail."""
+    cv2 = pytest.importorskip("cv2")
+    hs = np.zeros((181, 256, 3), np.uint8)
+    hs[..., 0] = np.arange(181)[:, None]
+    hs[..., 1] = np.arange(256)[None]
+    hs[..., 2] = 255
+    assert np.array_equal(post.hsv2rgb_u8(hs), cv2.cvtColor(hs, cv2.COLOR_HSV2RGB))
+    r = np.random.default_rng(0)
+    for w in (1, 7, 31, 32, 33, 53, 100):
+        x = r.integers(0, 256, (9, w, 3)).astype(np.uint8)
+        x[..., 0] %= 181
+        assert np.array_equal(post.hsv2rgb_u8(x), cv2.cvtColor(x, cv2.COLOR_HSV2RGB)), w
+
+
+def test_flo_lod_quality_oracle(golden, tmp_path):
+    g = golden("post2.npz")
+    _, fin, fe, frames, fl = _post2_inputs()
+    assert np.array_equal(np.frombuffer(post.flo_bytes(fin), np.uint8), g["flo_bytes"])
+    for name, f in (("lod_odd", fin), ("lod_even", fe)):
+        lods = post.lod_pyramid(f, 5)
+        assert len(lods) == 5
+        for i in range(1, 5):
+            assert np.array_equal(lods[i], g[f"{name}_{i}"]), (name, i)
+    assert np.array_equal(post.quality_frame(frames[0], frames[1], fl, 0.7), g["quality"])
+    assert np.array_equal(post.quality_frame(frames[0], frames[0], np.zeros_like(fl), 0.7), g["quality_same"])
+    small = np.ascontiguousarray(fl[::2, ::2][:16, :23])
+    assert np.array_equal(post.quality_frame(frames[0], frames[1], small, 0.7), g["quality_resized"])
+    # the product's file handler is host code: byte-identical .flo, lossless round trips, no GPU needed
+    from video_flow_ml_b200.storage import FlowCacheManager, FlowFileHandler
+    p = str(tmp_path / "a.flo")
+    FlowFileHandler.save_flow_flo(fin, p)
+    assert open(p, "rb").read() == g["flo_bytes"].tobytes()
+    assert np.array_equal(FlowFileHandler.load_flow_flo(p), fin)
+    open(p, "wb").write(b"XXXX" + b"\0" * 8)
+    with pytest.raises(ValueError):
+        FlowFileHandler.load_flow_flo(p)
+    m = FlowCacheManager()
+    d = str(tmp_path / "cache")
+    assert m.check_cache_exists(d, 2) == (False, None, [0, 1])
+    m.save_flow_to_cache(fin, d, 0, "both")
+    assert m.check_cache_exists(d, 2) == (False, None, [1])
+    m.save_flow_to_cache(torch.from_numpy(fe), d, 1, "npz")
+    assert m.check_cache_exists(d, 2) == (True, "npz", [])
+    assert np.array_equal(m.load_cached_flow(d, 0), fin) and np.array_equal(m.load_cached_flow(d, 0, "flo"), fin)
+    z = FlowFileHandler.load_flow_npz(os.path.join(d, "flow_frame_000001.npz"))
+    assert int(z["frame_idx"]) == 1 and tuple(z["shape"]) == fe.shape and np.array_equal(z["flow"], fe)
+    with pytest.raises(FileNotFoundError):
+        m.load_cached_flow(d, 5)
+    with pytest.raises(ValueError):
+        m.load_cached_flow(d, 0, "bmp")
+    m.save_flow_lods(post.lod_pyramid(fin, 3), d, 0)
+    assert np.array_equal(m.load_flow_lod(d, 0, 2), g["lod_odd_2"]) and not m.check_flow_lods_exist(d, 2, 3)
+
+
+def test_large_motion_and_fullsize_fixtures(golden):
+    """The drift weights (gain 1.0 + flow-head bias drift) against the unmodified reference wrapper: the oracle follows
+    coordinates that travel ~20 low-res texels through the border (mof_e2e_drift.npz), tolerance = a few times the
+    fixture's own 1-ulp sensitivity (stored in the fixture)."""
+    g = golden("mof_e2e_drift.npz")
+    assert float(g["ulp_sens"]) < 5e-3 and 0.5 < float(g["floor_fp16"]) < 5.0
+    sd = mof.mof_synthetic_weights(0, gain=1.0, drift=mof.DRIFT)
+    frames = cases.mof_case()
+    win = mof.frames_to_window(frames, 2, 5)
+    flow = mof.core_compute_flow(win, sd).permute(1, 2, 0).numpy()
+    assert np.abs(g["flow_2"]).max() > 100.0                       # >= 12 low-res texels of motion
+    assert np.sqrt(((flow - g["flow_2"]) ** 2).sum(-1)).max() <= 1e-2

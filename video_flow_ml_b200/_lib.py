@@ -43,8 +43,14 @@ PROTOTYPES = {
     "vfml_encode_gamedev": (i32, [vp, vp, i32, i32, f32, f32, f32, f32, vp]),
     "vfml_encode_mv_rg8": (i32, [vp, vp, i32, i32, f32, vp]),
     "vfml_decode_mv_rg8": (i32, [vp, vp, i32, i32, f32, vp]),
-    "vfml_taa": (i32, [vp, vp, vp, vp, i32, i32, f64, f64, i32, i32, vp]),
-    "vfml_taa_init": (i32, [vp, vp, i32, i32, vp]),
+    "vfml_encode_mv_rgb8": (i32, [vp, vp, i32, i32, f32, vp]),
+    "vfml_decode_mv_rgb8": (i32, [vp, vp, i32, i32, f32, vp]),
+    "vfml_encode_hsv": (i32, [vp, vp, i32, i32, vp, vp]),
+    "vfml_encode_torchvision": (i32, [vp, vp, i32, i32, i32, vp, vp]),
+    "vfml_lod_pyramid": (i32, [vp, i32, i32, C.POINTER(vp), i32, vp]),
+    "vfml_quality_frame": (i32, [vp, vp, vp, i32, i32, vp, i32, i32, f32, vp]),
+    "vfml_taa": (i32, [vp, i32, vp, vp, vp, i32, i32, f64, f64, i32, i32, vp]),
+    "vfml_taa_init": (i32, [vp, i32, vp, i32, i32, vp]),
     "vfml_gemm": (i32, [C.POINTER(GemmDesc), vp]),
     "vfml_gemm_uses_tensor_cores": (i32, [C.POINTER(GemmDesc)]),
     "vfml_dwconv_res_gelu": (i32, [vp, vp, i32, i32, i32, i32, i64, i64, vp, vp, i32, i32, vp]),

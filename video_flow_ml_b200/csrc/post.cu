@@ -55,13 +55,14 @@ __global__ void decode_rg8_kernel(const uint8_t* __restrict__ rgb, float2* __res
     }
 }
 
-__global__ void taa_init_kernel(const uint8_t* __restrict__ cur, double* __restrict__ out, int64_t n) {
+template <typename CurT>
+__global__ void taa_init_kernel(const CurT* __restrict__ cur, double* __restrict__ out, int64_t n) {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-        out[i] = (double)cur[i];
+        out[i] = (double)(float)cur[i];
 }
 
 struct TaaParams {
-    const uint8_t* cur;
+    const void* cur;        // [h, w, 3] u8, or fp32 (current_frame.astype(np.float32), taa_processor.py:64)
     const float* flow;
     const double* hist;
     double* out;
@@ -78,14 +79,16 @@ __device__ __forceinline__ double taa_coord(int g, float fl, int dim) {
     return fmin(fmax(v, 0.0), (double)(dim - 1));
 }
 
+template <typename CurT>
 __global__ void __launch_bounds__(256) taa_kernel(const TaaParams p) {
+    const CurT* __restrict__ cur = static_cast<const CurT*>(p.cur);
     const int64_t npix = (int64_t)p.h * p.w;
     const float a32 = (float)p.alpha, b32 = (float)p.one_minus_alpha;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < npix; i += (int64_t)gridDim.x * blockDim.x) {
         const int y = (int)(i / p.w), x = (int)(i - (int64_t)y * p.w);
         float c[3];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) c[k] = (float)p.cur[3 * i + k];
+        for (int k = 0; k < 3; ++k) c[k] = (float)cur[3 * i + k];
         double* o = p.out + 3 * i;
         if (p.mode == 0) {
             // simple EMA (:78-80): alpha * cur + (1 - alpha) * prev in the history's dtype
@@ -200,17 +203,18 @@ extern "C" int vfml_decode_mv_rg8(const uint8_t* rgb, float* flow, int height, i
     return VFML_OK;
 }
 
-extern "C" int vfml_taa_init(const uint8_t* cur, double* out, int h, int w, vfml_stream_t s) {
+extern "C" int vfml_taa_init(const void* cur, int cur_f32, double* out, int h, int w, vfml_stream_t s) {
     VFML_REQUIRE(h >= 0 && w >= 0, "taa_init: bad shape");
     const int64_t n = (int64_t)h * w * 3;
     if (n == 0) return VFML_OK;
     VFML_REQUIRE(cur && out, "taa_init: null pointer");
-    taa_init_kernel<<<ew_blocks(n), 256, 0, to_stream(s)>>>(cur, out, n);
+    if (cur_f32) taa_init_kernel<float><<<ew_blocks(n), 256, 0, to_stream(s)>>>(static_cast<const float*>(cur), out, n);
+    else taa_init_kernel<uint8_t><<<ew_blocks(n), 256, 0, to_stream(s)>>>(static_cast<const uint8_t*>(cur), out, n);
     VFML_LAUNCH_CHECK("taa_init");
     return VFML_OK;
 }
 
-extern "C" int vfml_taa(const uint8_t* cur, const float* flow, const double* history, double* out, int h, int w,
+extern "C" int vfml_taa(const void* cur, int cur_f32, const float* flow, const double* history, double* out, int h, int w,
                         double alpha, double sigma_color, int mode, int hist_f32, vfml_stream_t s) {
     VFML_REQUIRE(h >= 0 && w >= 0, "taa: bad shape");
     if ((int64_t)h * w == 0) return VFML_OK;
@@ -220,7 +224,8 @@ extern "C" int vfml_taa(const uint8_t* cur, const float* flow, const double* his
     VFML_REQUIRE(mode != 2 || (h >= 2 && w >= 2), "taa: bilateral mode needs at least 2x2 pixels");
     VFML_REQUIRE(history != out, "taa: out may not alias history");
     TaaParams p{cur, flow, history, out, h, w, alpha, 1.0 - alpha, 2.0 * (sigma_color * sigma_color * 0.1) + 1e-6, mode, hist_f32};
-    taa_kernel<<<ew_blocks((int64_t)h * w), 256, 0, to_stream(s)>>>(p);
+    if (cur_f32) taa_kernel<float><<<ew_blocks((int64_t)h * w), 256, 0, to_stream(s)>>>(p);
+    else taa_kernel<uint8_t><<<ew_blocks((int64_t)h * w), 256, 0, to_stream(s)>>>(p);
     VFML_LAUNCH_CHECK("taa");
     return VFML_OK;
 }

@@ -1,3 +1,3 @@
-from .taa_processor import TAAProcessor
+from .taa_processor import TAAComparisonProcessor, TAAProcessor, apply_taa_effect
 
-__all__ = ["TAAProcessor"]
+__all__ = ["TAAProcessor", "TAAComparisonProcessor", "apply_taa_effect"]

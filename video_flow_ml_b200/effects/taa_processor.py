@@ -1,4 +1,5 @@
-"""TAAProcessor on the libvfml TAA kernel (reference effects/taa_processor.py:20-330).
+"""TAAProcessor, TAAComparisonProcessor and apply_taa_effect on the libvfml TAA kernel (reference
+effects/taa_processor.py:20-262, :322-425).
 
 History stays on the device as float64 values; the dtype the reference would hold at each point
 (float32 on the first frame and in the simple / bilinear modes, float64 after the first
@@ -25,7 +26,9 @@ class TAAProcessor:
     def apply_taa(self, current_frame, flow_pixels=None, previous_taa_frame=None, alpha=None, use_flow=True,
                   use_bilateral=True, sequence_id='default', return_device=False):
         alpha = alpha if alpha is not None else self.alpha
-        cur = self._dev(current_frame, torch.uint8)
+        # uint8 frames are uploaded as bytes; anything else goes through float32 like the reference's
+        # current_frame.astype(np.float32) (:64), so float frames keep fractions and out-of-range values
+        cur = self._dev(current_frame, torch.uint8 if getattr(current_frame, "dtype", None) in (np.uint8, torch.uint8) else torch.float32)
         if previous_taa_frame is not None:
             is32 = getattr(previous_taa_frame, "dtype", None) in (np.float32, torch.float32)
             prev = (self._dev(previous_taa_frame, torch.float64), is32)
@@ -50,7 +53,8 @@ class TAAProcessor:
         return out.astype(np.float32) if state[1] else out
 
     def apply_simple_taa(self, current_frame, previous_taa_frame=None, alpha=None, sequence_id='simple'):
-        return self.apply_taa(current_frame, None, previous_taa_frame, alpha, use_flow=False, sequence_id=sequence_id)
+        return self.apply_taa(current_frame, None, previous_taa_frame, alpha, use_flow=False, use_bilateral=False,
+                              sequence_id=sequence_id)
 
     def reset_history(self, sequence_id=None):
         if sequence_id is None:
@@ -69,3 +73,31 @@ class TAAProcessor:
         if not 0.0 <= alpha <= 1.0:
             raise ValueError("Alpha must be between 0.0 and 1.0")
         self.alpha = alpha
+
+
+class TAAComparisonProcessor:
+    """Flow-based and simple TAA side by side (reference :322-391)."""
+
+    def __init__(self, alpha=0.1):
+        self.flow_taa = TAAProcessor(alpha)
+        self.simple_taa = TAAProcessor(alpha)
+
+    def apply_comparison(self, current_frame, flow_pixels=None, alpha=None):
+        flow_result = self.flow_taa.apply_taa(current_frame=current_frame, flow_pixels=flow_pixels, alpha=alpha,
+                                              use_flow=True, use_bilateral=True, sequence_id='flow')
+        simple_result = self.simple_taa.apply_simple_taa(current_frame=current_frame, alpha=alpha, sequence_id='simple')
+        return flow_result, simple_result
+
+    def reset_history(self):
+        self.flow_taa.reset_history()
+        self.simple_taa.reset_history()
+
+    def set_alpha(self, alpha):
+        self.flow_taa.set_alpha(alpha)
+        self.simple_taa.set_alpha(alpha)
+
+
+def apply_taa_effect(current_frame, flow_pixels=None, previous_taa_frame=None, alpha=0.1, use_flow=True):
+    """One-shot convenience call (reference :394-425)."""
+    return TAAProcessor(alpha).apply_taa(current_frame=current_frame, flow_pixels=flow_pixels,
+                                         previous_taa_frame=previous_taa_frame, alpha=alpha, use_flow=use_flow)

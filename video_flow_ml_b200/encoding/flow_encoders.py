@@ -1,8 +1,9 @@
-"""gamedev / motion-vectors-rg8 flow encoders on libvfml kernels, bit-exact with the numpy
-reference (encoding/flow_encoders.py:70-177, factory :430-483, helpers :485-540).
+"""Flow encoders / decoders on libvfml kernels, bit-exact with the numpy / torchvision / OpenCV arithmetic of the
+reference (encoding/flow_encoders.py: hsv :30-67, gamedev :70-117, motion-vectors-rg8 :120-177, motion-vectors-rgb8
+:180-364, torchvision :367-427, factory :430-483, helpers :485-540).
 
-``encode`` accepts a numpy array (uploaded, encoded, downloaded: the reference's signature) or a
-CUDA tensor (stays on the device: no host round trip when the flow was just computed there)."""
+``encode`` accepts a numpy array (uploaded, encoded, downloaded: the reference's signature) or a CUDA tensor (stays on the
+device: no host round trip when the flow was just computed there)."""
 from abc import ABC, abstractmethod
 
 import numpy as np
@@ -17,10 +18,25 @@ def _to_device(flow, device="cuda"):
     return torch.from_numpy(np.ascontiguousarray(flow, dtype=np.float32)).to(device), False
 
 
+def _u8_to_device(img, device="cuda"):
+    if isinstance(img, torch.Tensor):
+        return img.contiguous(), True
+    return torch.from_numpy(np.ascontiguousarray(img, dtype=np.uint8)).to(device), False
+
+
 class FlowEncoder(ABC):
     @abstractmethod
     def encode(self, flow, width, height):
         """flow (H, W, 2) -> RGB (H, W, 3) uint8"""
+
+
+class HSVFlowEncoder(FlowEncoder):
+    """Hue = direction, saturation = magnitude / max magnitude, value = 255 (reference :30-67)."""
+
+    def encode(self, flow, width, height):
+        t, on_dev = _to_device(flow)
+        out = ops.encode_hsv(t)
+        return out if on_dev else out.cpu().numpy()
 
 
 class GamedevFlowEncoder(FlowEncoder):
@@ -46,15 +62,50 @@ class MotionVectorsRG8FlowEncoder(FlowEncoder):
         return out if on_dev else out.cpu().numpy()
 
     def decode(self, encoded_flow):
-        if isinstance(encoded_flow, torch.Tensor):
-            return ops.decode_mv_rg8(encoded_flow.contiguous(), self.clamp_range)
-        t = torch.from_numpy(np.ascontiguousarray(encoded_flow, dtype=np.uint8)).cuda()
-        return ops.decode_mv_rg8(t, self.clamp_range).cpu().numpy()
+        t, on_dev = _u8_to_device(encoded_flow)
+        out = ops.decode_mv_rg8(t, self.clamp_range)
+        return out if on_dev else out.cpu().numpy()
+
+
+class MotionVectorsRGB8FlowEncoder(FlowEncoder):
+    """Direction in R, G and sqrt(1 - |d|^2) in B: the reference's module-level ``method = 'rgb+'`` (:10, :242-262)."""
+
+    def __init__(self, clamp_range=32.0):
+        self.clamp_range = clamp_range
+
+    def encode(self, flow, width, height):
+        t, on_dev = _to_device(flow)
+        out = ops.encode_mv_rgb8(t, self.clamp_range)
+        return out if on_dev else out.cpu().numpy()
+
+    def decode(self, encoded_flow):
+        t, on_dev = _u8_to_device(encoded_flow)
+        out = ops.decode_mv_rgb8(t, self.clamp_range)
+        return out if on_dev else out.cpu().numpy()
+
+
+class TorchvisionFlowEncoder(FlowEncoder):
+    """Colour-wheel format of torchvision.utils.flow_to_image, including the reference's final ``(img * 255).astype(uint8)``
+    on the already-uint8 image (:425), which wraps modulo 256.  The fallback encoder argument is kept for signature
+    compatibility; the kernel needs no torchvision."""
+
+    def __init__(self, fallback_encoder=None):
+        self.fallback_encoder = fallback_encoder or HSVFlowEncoder()
+
+    def encode(self, flow, width, height):
+        t, on_dev = _to_device(flow)
+        out = ops.encode_torchvision(t, ref_wrap=True)
+        return out if on_dev else out.cpu().numpy()
 
 
 class FlowEncoderFactory:
-    # hsv / torchvision / motion-vectors-rgb8 of the reference are "next" items
-    _encoders = {'gamedev': GamedevFlowEncoder, 'motion-vectors-rg8': MotionVectorsRG8FlowEncoder}
+    _encoders = {
+        'hsv': HSVFlowEncoder,
+        'gamedev': GamedevFlowEncoder,
+        'torchvision': TorchvisionFlowEncoder,
+        'motion-vectors-rg8': MotionVectorsRG8FlowEncoder,
+        'motion-vectors-rgb8': MotionVectorsRGB8FlowEncoder,
+    }
 
     @classmethod
     def create_encoder(cls, format_name, **kwargs):
@@ -79,14 +130,16 @@ def encode_flow(flow, width, height, format_name='gamedev'):
     return FlowEncoderFactory.create_encoder(format_name).encode(flow, width, height)
 
 
-def encode_motion_vectors(flow, clamp_range=64.0, format_variant='rg8'):
-    if format_variant.lower() != 'rg8':
-        raise NotImplementedError("only the rg8 motion-vector variant is implemented in this build")
+def _mv_encoder(clamp_range, format_variant):
+    if format_variant.lower() == 'rg8':
+        return MotionVectorsRG8FlowEncoder(clamp_range=clamp_range)
+    return MotionVectorsRGB8FlowEncoder(clamp_range=clamp_range)       # the reference's default (:502-528)
+
+
+def encode_motion_vectors(flow, clamp_range=64.0, format_variant='rgb8'):
     h, w = flow.shape[:2]
-    return MotionVectorsRG8FlowEncoder(clamp_range=clamp_range).encode(flow, w, h)
+    return _mv_encoder(clamp_range, format_variant).encode(flow, w, h)
 
 
-def decode_motion_vectors(encoded_flow, clamp_range=64.0, format_variant='rg8'):
-    if format_variant.lower() != 'rg8':
-        raise NotImplementedError("only the rg8 motion-vector variant is implemented in this build")
-    return MotionVectorsRG8FlowEncoder(clamp_range=clamp_range).decode(encoded_flow)
+def decode_motion_vectors(encoded_flow, clamp_range=64.0, format_variant='rgb8'):
+    return _mv_encoder(clamp_range, format_variant).decode(encoded_flow)

@@ -300,24 +300,116 @@ def decode_mv_rg8(rgb, clamp=64.0):
     return out
 
 
+def _u8_like(flow):
+    H, W, two = flow.shape
+    if two != 2:
+        raise ValueError("flow must be [H, W, 2]")
+    return H, W, torch.empty((H, W, 3), dtype=torch.uint8, device=flow.device)
+
+
+def encode_mv_rgb8(flow, clamp=32.0):
+    """flow [H, W, 2] fp32 CUDA -> [H, W, 3] u8: direction (R, G) + sqrt(1 - |d|^2) (B), flow_encoders.py:242-262."""
+    _cuda(flow)
+    _f32c(flow, "flow")
+    H, W, out = _u8_like(flow)
+    _lib.check(_lib.load().vfml_encode_mv_rgb8(_p(flow), _p(out), H, W, float(clamp), _stream()), "encode_mv_rgb8")
+    return out
+
+
+def decode_mv_rgb8(rgb, clamp=32.0):
+    _cuda(rgb)
+    if rgb.dtype != torch.uint8 or not rgb.is_contiguous() or rgb.dim() != 3 or rgb.shape[2] != 3:
+        raise ValueError("decode_mv_rgb8: expected contiguous uint8 [H, W, 3]")
+    H, W, _ = rgb.shape
+    out = torch.empty((H, W, 2), dtype=torch.float32, device=rgb.device)
+    _lib.check(_lib.load().vfml_decode_mv_rgb8(_p(rgb), _p(out), H, W, float(clamp), _stream()), "decode_mv_rgb8")
+    return out
+
+
+def encode_hsv(flow):
+    """HSVFlowEncoder.encode (flow_encoders.py:38-67) incl. OpenCV's HSV -> RGB."""
+    _cuda(flow)
+    _f32c(flow, "flow")
+    H, W, out = _u8_like(flow)
+    scratch = torch.empty(4, dtype=torch.uint8, device=flow.device)
+    _lib.check(_lib.load().vfml_encode_hsv(_p(flow), _p(out), H, W, _p(scratch), _stream()), "encode_hsv")
+    return out
+
+
+def encode_torchvision(flow, ref_wrap=True):
+    """TorchvisionFlowEncoder.encode (flow_encoders.py:399-427).  ref_wrap=False gives torchvision's flow_to_image itself."""
+    _cuda(flow)
+    _f32c(flow, "flow")
+    H, W, out = _u8_like(flow)
+    scratch = torch.empty(4, dtype=torch.uint8, device=flow.device)
+    _lib.check(_lib.load().vfml_encode_torchvision(_p(flow), _p(out), H, W, int(bool(ref_wrap)), _p(scratch), _stream()),
+               "encode_torchvision")
+    return out
+
+
+def lod_pyramid(flow, num_lods=5):
+    """LODGenerator.generate_lods (storage/cache_manager.py:77-161): [flow, lod1, ...], level l+1 = [ceil(h/2), ceil(w/2), 2]."""
+    _cuda(flow)
+    _f32c(flow, "flow")
+    if flow.dim() != 3 or flow.shape[2] != 2 or flow.shape[0] < 1 or flow.shape[1] < 1:
+        raise ValueError("lod_pyramid: flow must be a non-empty [H, W, 2] tensor")
+    lods = [flow]
+    while len(lods) < num_lods:
+        src = lods[-1]
+        n = min(4, num_lods - len(lods))
+        h, w = src.shape[:2]
+        new = []
+        for _ in range(n):
+            h, w = (h + 1) // 2, (w + 1) // 2
+            new.append(torch.empty((h, w, 2), dtype=torch.float32, device=flow.device))
+        arr = (C.c_void_p * n)(*[t.data_ptr() for t in new])
+        _lib.check(_lib.load().vfml_lod_pyramid(_p(src), src.shape[0], src.shape[1], arr, n, _stream()), "lod_pyramid")
+        lods += new
+    return lods
+
+
+def quality_frame(frame1, frame2, flow, threshold):
+    """generate_quality_frame_gpu (correction_worker.py:175-208): u8 frames [H, W, 3], fp32 flow [h, w, 2] -> u8 [H, W, 3]."""
+    _cuda(frame1, frame2, flow)
+    _f32c(flow, "flow")
+    for f in (frame1, frame2):
+        if f.dtype != torch.uint8 or not f.is_contiguous() or f.dim() != 3 or f.shape[2] != 3:
+            raise ValueError("quality_frame: frames must be contiguous uint8 [H, W, 3]")
+    if frame1.shape != frame2.shape or flow.dim() != 3 or flow.shape[2] != 2:
+        raise ValueError("quality_frame: shape mismatch")
+    H, W, _ = frame1.shape
+    out = torch.empty((H, W, 3), dtype=torch.uint8, device=frame1.device)
+    _lib.check(_lib.load().vfml_quality_frame(_p(frame1), _p(frame2), _p(flow), flow.shape[0], flow.shape[1], _p(out), H, W,
+                                              float(threshold), _stream()), "quality_frame")
+    return out
+
+
+def _taa_cur(cur):
+    if cur.dtype not in (torch.uint8, torch.float32) or cur.dim() != 3 or cur.shape[2] != 3:
+        raise ValueError("taa: the current frame must be a uint8 or float32 [H, W, 3] tensor")
+    return cur.contiguous(), int(cur.dtype == torch.float32)
+
+
 def taa_init(cur):
     _cuda(cur)
+    cur, is32 = _taa_cur(cur)
     H, W, _ = cur.shape
     out = torch.empty((H, W, 3), dtype=torch.float64, device=cur.device)
-    _lib.check(_lib.load().vfml_taa_init(_p(cur), _p(out), H, W, _stream()), "taa_init")
+    _lib.check(_lib.load().vfml_taa_init(_p(cur), is32, _p(out), H, W, _stream()), "taa_init")
     return out
 
 
 def taa(cur, flow, history, alpha, sigma_color, mode, hist_f32):
-    """cur [H,W,3] u8, flow [H,W,2] fp32 or None, history [H,W,3] f64 -> new [H,W,3] f64."""
+    """cur [H,W,3] u8 or fp32, flow [H,W,2] fp32 or None, history [H,W,3] f64 -> new [H,W,3] f64."""
     _cuda(cur, flow, history)
+    cur, is32 = _taa_cur(cur)
     H, W, _ = cur.shape
-    if cur.dtype != torch.uint8 or history.dtype != torch.float64 or history.shape != cur.shape:
+    if history.dtype != torch.float64 or history.shape != cur.shape:
         raise ValueError("taa: bad tensor types")
     if flow is not None:
         _f32c(flow, "flow")
     out = torch.empty_like(history)
-    _lib.check(_lib.load().vfml_taa(_p(cur.contiguous()), _p(flow), _p(history.contiguous()), _p(out), H, W, float(alpha),
+    _lib.check(_lib.load().vfml_taa(_p(cur), is32, _p(flow), _p(history.contiguous()), _p(out), H, W, float(alpha),
                                     float(sigma_color), int(mode), int(bool(hist_f32)), _stream()), "taa")
     return out
 
