@@ -51,6 +51,8 @@ int vfml_version(void);
 const char* vfml_last_error(void);
 /* Number of kernels this library has launched since it was loaded (all threads). */
 uint64_t vfml_launch_count(void);
+/* SM count of the calling thread's current CUDA device (grids are sized from it; 148 on B200). */
+int vfml_device_sms(void);
 
 /* ---------------------------------------------------------------------------------
  * Layout conversion.  src [n, c, hw] fp32 planar  <->  rows [n*hw, pitch] of `dtype`.

@@ -63,7 +63,7 @@ def corr_lookup_perm(device=None):
     return real(device)
 
 
-def corr_volume_pyramid_tiled(f1, f2, workspace=None):
+def corr_volume_pyramid_tiled(f1, f2, workspace=None, out=None):
     return corr_volume_pyramid(f1, f2, 4)
 
 

@@ -27,6 +27,7 @@ PROTOTYPES = {
     "vfml_version": (i32, []),
     "vfml_last_error": (C.c_char_p, []),
     "vfml_launch_count": (C.c_uint64, []),
+    "vfml_device_sms": (i32, []),
     "vfml_nchw_to_rows": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp]),
     "vfml_rows_to_nchw": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp]),
     "vfml_corr_volume_workspace": (sz, [i32, i32, i32, i32, i32]),

@@ -57,6 +57,16 @@ __device__ __forceinline__ float gelu_erf(float x) {
     return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
 }
 
+// SM count of the calling thread's current device (cached per device; 148 on B200) and the device's index
+int device_sms();
+int device_index();
+// Per-device one-time setup (cudaFuncSetAttribute is per device): a static `PerDevice<bool> done;` reads as false the
+// first time each device gets here.
+template <typename T> struct PerDevice {
+    T v[64] = {};
+    T& get() { return v[device_index() & 63]; }
+};
+
 inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
 inline bool valid_dtype(int d) { return d == VFML_F32 || d == VFML_F16; }

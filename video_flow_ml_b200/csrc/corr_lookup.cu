@@ -236,23 +236,23 @@ static int launch_lookup(const LookupParams& p, int radius, cudaStream_t st) {
     const int P = p.h * p.w;
     if (radius == LK_R && p.layout == VFML_ROWS) {
         const int64_t total = (int64_t)p.n_frames * P * p.n_sets;
-        const int blocks = (int)std::min<int64_t>((total + 3) / 4, 148 * 8);
+        const int blocks = (int)std::min<int64_t>((total + 3) / 4, device_sms() * 8);
         corr_lookup_rows_kernel<TV, TO><<<blocks, 128, 0, st>>>(p);
         VFML_LAUNCH_CHECK("corr_lookup_rows");
     } else if (radius == LK_R) {
         auto kern = corr_lookup_nchw_kernel<TV, TO>;
         const size_t smem = (LK_TP * (LK_MAXL * LK_NTAP + 1) + LK_WARPS * LK_MAXL * LK_NTEX_PAD) * sizeof(float);
-        static bool attr_done = false;
-        if (!attr_done) {
+        static PerDevice<bool> attr_done;
+        if (!attr_done.get()) {
             VFML_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            attr_done = true;
+            attr_done.get() = true;
         }
         kern<<<p.n_frames * ((P + LK_TP - 1) / LK_TP), LK_WARPS * 32, smem, st>>>(p);
         VFML_LAUNCH_CHECK("corr_lookup_nchw");
     } else {
         const int win = 2 * radius + 1;
         const int64_t total = (int64_t)p.n_frames * P * p.num_levels * win * win;
-        const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
+        const int blocks = (int)std::min<int64_t>((total + 255) / 256, device_sms() * 16);
         corr_lookup_generic_kernel<TV, TO><<<blocks, 256, 0, st>>>(p, radius);
         VFML_LAUNCH_CHECK("corr_lookup_generic");
     }

@@ -406,12 +406,12 @@ extern "C" int vfml_corr_tile_pyramid(const void* vol0, int64_t rows, int h, int
     p.rows = rows;
     const size_t smem = (size_t)off * sizeof(__half);
     VFML_REQUIRE(smem <= 200 * 1024, "corr_tile_pyramid: %d x %d does not fit shared memory", h, w);
-    static size_t attr = 0;
-    if (smem > 48 * 1024 && smem > attr) {
+    static PerDevice<size_t> attr;
+    if (smem > 48 * 1024 && smem > attr.get()) {
         VFML_CUDA(cudaFuncSetAttribute(corr_tile_pyramid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr = smem;
+        attr.get() = smem;
     }
-    const int blocks = (int)std::min<int64_t>(rows, 148 * 16);
+    const int blocks = (int)std::min<int64_t>(rows, device_sms() * 16);
     corr_tile_pyramid_kernel<<<blocks, 256, smem, to_stream(s)>>>(p);
     VFML_LAUNCH_CHECK("corr_tile_pyramid");
     return VFML_OK;
@@ -487,13 +487,13 @@ extern "C" int vfml_corr_lookup_tiled(const void* const* levels_a, const void* c
     p.total = (int)total;
     p.n_batches = (p.total + TL_UNITS - 1) / TL_UNITS;
     p.out_pitch = out_pitch;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static PerDevice<bool> attr_done;
+    if (!attr_done.get()) {
         VFML_CUDA(cudaFuncSetAttribute(corr_lookup_tiled_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL_SMEM));
         VFML_CUDA(cudaFuncSetAttribute(corr_lookup_tiled_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL_SMEM));
-        attr_done = true;
+        attr_done.get() = true;
     }
-    const int blocks = std::min(148 * TL_CTAS_PER_SM, (p.n_batches + TL_WARPS - 1) / TL_WARPS);
+    const int blocks = std::min(device_sms() * TL_CTAS_PER_SM, (p.n_batches + TL_WARPS - 1) / TL_WARPS);
     if (math_f32) corr_lookup_tiled_kernel<true><<<blocks, TL_WARPS * 32, TL_SMEM, to_stream(s)>>>(p);
     else corr_lookup_tiled_kernel<false><<<blocks, TL_WARPS * 32, TL_SMEM, to_stream(s)>>>(p);
     VFML_LAUNCH_CHECK("corr_lookup_tiled");

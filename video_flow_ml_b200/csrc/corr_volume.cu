@@ -118,7 +118,7 @@ static int run_volume(const float* f1, const float* f2, int n_pairs, int C, int 
         const int64_t rows = (int64_t)n_pairs * P;
         const int64_t total = rows * (hi / 2) * (wi / 2);
         if (total > 0) {
-            const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 32);
+            const int blocks = (int)std::min<int64_t>((total + 255) / 256, device_sms() * 32);
             corr_pool_kernel<TV><<<blocks, 256, 0, st>>>(reinterpret_cast<const TV*>(levels[l - 1]),
                                                         reinterpret_cast<TV*>(levels[l]), rows, hi, wi);
             VFML_LAUNCH_CHECK("corr_pool");
@@ -172,7 +172,7 @@ static int run_volume_tc(const float* f1, const float* f2, int n_pairs, int C, i
         const int64_t rows = (int64_t)n_pairs * P;
         const int64_t total = rows * (hi / 2) * (wi / 2);
         if (total > 0) {
-            const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 32);
+            const int blocks = (int)std::min<int64_t>((total + 255) / 256, device_sms() * 32);
             corr_pool_kernel<__half><<<blocks, 256, 0, st>>>(reinterpret_cast<const __half*>(levels[l - 1]),
                                                             reinterpret_cast<__half*>(levels[l]), rows, hi, wi);
             VFML_LAUNCH_CHECK("corr_pool");

@@ -131,10 +131,10 @@ static int launch_dw_tile(const T* x, T* y, int n_img, int h, int w, int C, int6
     constexpr int TWX = DW_TX + K - 1, TWY = DW_TY + K - 1;
     const size_t smem = (size_t)TWY * TWX * 32 * sizeof(typename V::ld_t);
     auto kern = dwconv_tile_kernel<T, K>;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static PerDevice<bool> attr_done;
+    if (!attr_done.get()) {
         VFML_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_done = true;
+        attr_done.get() = true;
     }
     const int tiles_x = cdiv(w, DW_TX), tiles_y = cdiv(h, DW_TY);
     dim3 grid(tiles_x * tiles_y * n_img, cdiv(C, 32 * V::VEC));

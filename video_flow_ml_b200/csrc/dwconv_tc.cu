@@ -358,11 +358,11 @@ static int launch_dw_tc(const __half* x, __half* y, int n_img, int h, int w, int
     static const kern_t kerns[4] = {dwconv_tc_kernel<K, 0, TH>, dwconv_tc_kernel<K, 1, TH>, dwconv_tc_kernel<K, 2, TH>,
                                     dwconv_tc_kernel<K, 3, TH>};
     using Cfg = DtCfg<K, TH>;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static PerDevice<bool> attr_done;
+    if (!attr_done.get()) {
         for (int i = 0; i < 4; ++i)
             VFML_CUDA(cudaFuncSetAttribute(kerns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
-        attr_done = true;
+        attr_done.get() = true;
     }
     const int tiles_x = cdiv(w, DT_TW), tiles_y = cdiv(h, TH);
     dim3 grid(tiles_x * tiles_y * n_img, cdiv(C, DT_CG));
@@ -390,12 +390,7 @@ static int launch_dw_tc_any(const __half* x, __half* y, int n_img, int h, int w,
     // previous configuration, kept for A/B.
     static const int mode = getenv("VFML_DW_TMA") ? atoi(getenv("VFML_DW_TMA")) & 3 : 3;
     static const int th_env = getenv("VFML_DW_TH") ? atoi(getenv("VFML_DW_TH")) : 32;
-    static int num_sms = 0;
-    if (!num_sms) {
-        int dev = 0;
-        VFML_CUDA(cudaGetDevice(&dev));
-        VFML_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
-    }
+    const int num_sms = device_sms();
     int th = th_env;
     if (th != 32 && th != 64) {
         const int64_t per = (int64_t)cdiv(w, DT_TW) * n_img * cdiv(C, DT_CG);
@@ -421,7 +416,7 @@ extern "C" int vfml_dwconv_pack_weights(const float* weight, int C, int k, void*
     VFML_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 15) == 0, "dwconv_pack_weights: packed must be 16-byte aligned");
     const int groups = cdiv(C, DT_CG);
     const int total = groups * DT_CG * k * 128;
-    const int blocks = std::min(cdiv(total, 256), 148 * 8);
+    const int blocks = std::min(cdiv(total, 256), device_sms() * 8);
     if (k == 15) dwconv_pack_kernel<15><<<blocks, 256, 0, to_stream(s)>>>(weight, reinterpret_cast<__half*>(packed), C, groups);
     else dwconv_pack_kernel<7><<<blocks, 256, 0, to_stream(s)>>>(weight, reinterpret_cast<__half*>(packed), C, groups);
     VFML_LAUNCH_CHECK("dwconv_pack");

@@ -15,8 +15,8 @@
 // zero-filled by TMA, so no shape needs padding.
 //
 // The epilogue is the co-bottleneck of these small-K GEMMs (K = 128..768), so its math is packed:
-// fp32 pairs through fma.rn.f32x2, and GELU through a degree-12 polynomial in x^2 of
-// (Phi(x) - 1/2) / x on |x| <= 5 (max abs error 2e-6, no MUFU ops).
+// fp32 pairs through fma.rn.f32x2, and GELU in its tanh form (gelu_poly.cuh: one MUFU tanh.approx plus six packed
+// FMA-pipe operations per pair; the MUFU-free degree-12 polynomial is kept behind -DVFML_GELU_MUFU=0).
 #include <cuda.h>
 #include <stdlib.h>
 
@@ -576,13 +576,12 @@ static const TcKernel tc_kernels[] = {
 constexpr int TC_NUM_KERNELS = sizeof(tc_kernels) / sizeof(tc_kernels[0]);
 
 int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st) {
-    static int num_sms = 0;
-    if (!num_sms) {
-        int dev = 0;
-        VFML_CUDA(cudaGetDevice(&dev));
-        VFML_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+    const int num_sms = device_sms();
+    static PerDevice<bool> attr_done;
+    if (!attr_done.get()) {
         for (int i = 0; i < TC_NUM_KERNELS; ++i)
             VFML_CUDA(cudaFuncSetAttribute(tc_kernels[i].fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 512));
+        attr_done.get() = true;
     }
     const size_t SMEM_MAX = 227 * 1024 - 512;
     const size_t a_bytes = TC_BM * TC_BK * 2;
@@ -660,10 +659,13 @@ int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st) {
     const int64_t num_tiles = (int64_t)p.m_tiles * p.n_tiles * d.batch;
     const int grid = b_res ? std::max(1, num_sms / n_tiles) * n_tiles : (int)std::min<int64_t>(num_tiles, num_sms);
     static const bool trace = getenv("VFML_GEMM_TRACE") != nullptr;
-    static long long* trace_buf = nullptr;
+    constexpr int TRACE_MAX_CTAS = 1024;      // debug buffer: one 8-counter record per CTA of the persistent grid
+    static PerDevice<long long*> trace_bufs;
+    long long*& trace_buf = trace_bufs.get();
     if (trace) {
-        if (!trace_buf) VFML_CUDA(cudaMalloc(&trace_buf, 148 * 8 * sizeof(long long)));
-        VFML_CUDA(cudaMemsetAsync(trace_buf, 0, 148 * 8 * sizeof(long long), st));
+        VFML_REQUIRE(grid <= TRACE_MAX_CTAS, "gemm_tc: VFML_GEMM_TRACE supports at most %d CTAs", TRACE_MAX_CTAS);
+        if (!trace_buf) VFML_CUDA(cudaMalloc(&trace_buf, TRACE_MAX_CTAS * 8 * sizeof(long long)));
+        VFML_CUDA(cudaMemsetAsync(trace_buf, 0, (size_t)grid * 8 * sizeof(long long), st));
         p.trace = trace_buf;
     }
     // programmatic dependent launch: this kernel's prologue (and its resident weight tile) overlaps the tail of the
@@ -694,8 +696,8 @@ int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st) {
     }
     VFML_LAUNCH_CHECK("gemm_tc");
     if (trace) {      // debug only: synchronises
-        long long h[148 * 8];
-        VFML_CUDA(cudaMemcpyAsync(h, trace_buf, sizeof(h), cudaMemcpyDeviceToHost, st));
+        static long long h[TRACE_MAX_CTAS * 8];
+        VFML_CUDA(cudaMemcpyAsync(h, trace_buf, (size_t)grid * 8 * sizeof(long long), cudaMemcpyDeviceToHost, st));
         VFML_CUDA(cudaStreamSynchronize(st));
         double a[8] = {0};
         for (int c = 0; c < grid; ++c)

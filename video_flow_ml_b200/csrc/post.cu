@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(256) taa_kernel(const TaaParams p) {
     }
 }
 
-static inline int ew_blocks(int64_t n) { return (int)std::min<int64_t>((n + 255) / 256, 148 * 16); }
+static inline int ew_blocks(int64_t n) { return (int)std::min<int64_t>((n + 255) / 256, device_sms() * 16); }
 
 }  // namespace vfml
 

@@ -13,14 +13,7 @@
 
 namespace vfml {
 
-static int sm_count() {
-    static int n[64] = {0};
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
-    if (!n[dev]) cudaDeviceGetAttribute(&n[dev], cudaDevAttrMultiProcessorCount, dev);
-    return n[dev] > 0 ? n[dev] : 148;
-}
-static inline int ew_blocks2(int64_t n) { return (int)std::min<int64_t>((n + 255) / 256, (int64_t)sm_count() * 16); }
+static inline int ew_blocks2(int64_t n) { return (int)std::min<int64_t>((n + 255) / 256, (int64_t)device_sms() * 16); }
 
 // rgb * 255 -> nan_to_num(nan=0, +inf=255, -inf=0) -> astype(uint8)          flow_encoders.py:292-295
 __device__ __forceinline__ uint8_t to_u8_scrub(float v) {

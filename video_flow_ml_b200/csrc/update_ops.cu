@@ -317,7 +317,7 @@ __global__ void im2col3x3_kernel(const T* __restrict__ x, T* __restrict__ out, i
     }
 }
 
-static inline int ew_blocks(int64_t n) { return (int)std::min<int64_t>((n + 255) / 256, 148 * 32); }
+static inline int ew_blocks(int64_t n) { return (int)std::min<int64_t>((n + 255) / 256, device_sms() * 32); }
 
 int dwconv_tiled(const void* x, void* y, int n_img, int h, int w, int C, int64_t px, int64_t py, const float* wgt,
                  const float* bias, int k, int dtype, cudaStream_t st);
@@ -430,7 +430,7 @@ extern "C" int vfml_layer_norm_rows(const void* x, void* y, int64_t rows, int C,
     auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
     VFML_REQUIRE(al(x) && al(y) && al(gamma) && al(beta), "layer_norm_rows: pointers must be 16-byte aligned");
     const int vpl = (C / E + 31) / 32;           // 16-byte vectors per lane
-    const int blocks = (int)std::min<int64_t>(cdiv(rows, 8), 148 * 16);
+    const int blocks = (int)std::min<int64_t>(cdiv(rows, 8), device_sms() * 16);
 #define VFML_LN_CASE(V)                                                                                                             \
     case V:                                                                                                                         \
         DISPATCH_T(dtype, (layer_norm_rows_kernel<float, V><<<blocks, 256, 0, to_stream(s)>>>((const float*)x, (float*)y, rows, C, ld_x, ld_y, (const float*)gamma, (const float*)beta, eps)), \
@@ -457,7 +457,7 @@ extern "C" int vfml_motion_glue(const float* fcoords, const float* bcoords, void
     VFML_REQUIRE(fcoords && bcoords && x400 && f128 && mf && convf1_w && convf1_b, "motion_glue: null pointer");
     GlueParams p{fcoords, bcoords, x400, pitch400, f128, pitch128, mf, pitch_mf, mf_col, convf1_w, convf1_b, n_frames, h, w};
     const int64_t total = (int64_t)n_frames * h * w;
-    const int blocks = (int)std::min<int64_t>(cdiv(total, 8), 148 * 16);
+    const int blocks = (int)std::min<int64_t>(cdiv(total, 8), device_sms() * 16);
     DISPATCH_T(dtype, (motion_glue_kernel<float><<<blocks, 256, 0, to_stream(s)>>>(p)),
                (motion_glue_kernel<__half><<<blocks, 256, 0, to_stream(s)>>>(p)));
     VFML_LAUNCH_CHECK("motion_glue");

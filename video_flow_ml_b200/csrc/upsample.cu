@@ -175,7 +175,7 @@ extern "C" int vfml_convex_upsample8(const float* flow, const void* mask, int ma
     if (mask_layout == VFML_NCHW) {
         convex_upsample8_nchw_kernel<<<cdiv(total, 128), 128, 0, st>>>(p);
     } else {
-        const int blocks = (int)std::min<int64_t>(cdiv(total, 8), 148 * 16);
+        const int blocks = (int)std::min<int64_t>(cdiv(total, 8), device_sms() * 16);
         if (mask_dtype == VFML_F32) convex_upsample8_kernel<float><<<blocks, 256, 0, st>>>(p);
         else convex_upsample8_kernel<__half><<<blocks, 256, 0, st>>>(p);
     }

@@ -139,6 +139,10 @@ class MemFlowEngine(MOFEngine):
                 "mask": self._rows_buf(P, 576, torch.float32),
                 "graphs": {},
             }
+            # split-K partial sums of the read-out, sized for the worst memory length: the graphs captured per memory
+            # length hold this buffer's address, so it is never replaced afterwards
+            s_max = max(self._splits(P, k * P) for k in range(1, 2 + self.max_stored))
+            ws["partial0"] = torch.empty(s_max * P * 128, dtype=torch.float32, device=self.dev)
             self._ws = {key: ws}
             self.n_stored = 0         # a new frame size invalidates the stored keys / values
         return ws
@@ -224,7 +228,7 @@ class MemFlowEngine(MOFEngine):
         if g is None:
             static = [t.clone() for t in args]
             self._body(ws, *static, h, w, self.n_stored)            # eager warm-up; only the current-frame memory slot is written
-            torch.cuda.synchronize()
+            torch.cuda.synchronize(self.dev)
             graph = torch.cuda.CUDAGraph()
             n0 = _lib.launch_count()
             with torch.cuda.graph(graph):
@@ -245,6 +249,10 @@ class MemFlowEngine(MOFEngine):
             raise ValueError(f"step expects images [1, 2, 3, H, W], got {tuple(images.shape)}")
         if images.shape[-1] % 8 or images.shape[-2] % 8:
             raise ValueError("H and W must be multiples of 8 (pad with InputPadder first)")
+        with self._guard():
+            return self._step(images, end, flow_init, crop)
+
+    def _step(self, images, end, flow_init, crop):
         o = self.ops
         self.curr_ti += 1
         is_mem_frame = (self.curr_ti - self.last_mem_ti >= self.mem_every) and not end

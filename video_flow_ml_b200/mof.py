@@ -32,6 +32,19 @@ def _pad8(c):
     return (c + 7) // 8 * 8
 
 
+_SMS = {}
+
+
+def _sm_count():
+    """SM count of the current CUDA device (148 on B200; also the answer without a device, for the CPU data-flow tests)."""
+    if not torch.cuda.is_available():
+        return 148
+    d = torch.cuda.current_device()
+    if d not in _SMS:
+        _SMS[d] = torch.cuda.get_device_properties(d).multi_processor_count
+    return _SMS[d]
+
+
 def _pad_act(c):
     """Row pitch of activation buffers: a multiple of 16 elements, so that every row of an fp16 buffer starts on a 32-byte
     sector and the GEMM epilogue's 16-column pieces are single 256-bit stores (gemm_tc.cu)."""
@@ -118,7 +131,8 @@ class MOFEngine:
         enc_dt = encoder_dtype or torch.float32
         self.fnet = TwinsStage01(sd, "fnet.svt", dev, enc_dt) if "fnet.svt.patch_embeds.0.proj.weight" in sd else None
         self.cnet = TwinsStage01(sd, "cnet.svt", dev, enc_dt) if "cnet.svt.patch_embeds.0.proj.weight" in sd else None
-        self._ws = {}
+        self._ws = {}                    # (Fc, h, w) -> workspace; a small LRU (tile mode alternates between 2-3 shapes)
+        self.max_workspaces = int(os.environ.get("VFML_MAX_WORKSPACES", "3"))
         self.use_graph = use_graph
         self.lookup_math_f32 = False     # fp16x2 interpolation: 2.43e-2 px vs 2.37e-2 px (fp32) end to end, 8 % faster
         self.graph_launches = 0          # kernels executed through CUDA-graph replays (not seen by vfml_launch_count)
@@ -130,9 +144,19 @@ class MOFEngine:
         return torch.zeros((n, pitch), dtype=dtype or self.dt, device=self.dev)[:, :c]
 
     def _workspace(self, Fc, h, w):
+        """Buffers (and, once captured, the CUDA graph) of one window shape.  Kept in an LRU of `max_workspaces` shapes:
+        a ragged tile grid (4K: 1280x1280 and 1280x880 tiles) or a change of sequence length switches shape without
+        dropping the other shape's multi-GB workspace and re-capturing its ~1300-launch graph."""
         key = (Fc, h, w)
-        ws = self._ws.get(key)
-        if ws is None:
+        ws = self._ws.pop(key, None)
+        if ws is not None:
+            self._ws[key] = ws            # most recently used last
+            return ws
+        while len(self._ws) >= max(1, self.max_workspaces):
+            old = self._ws.pop(next(iter(self._ws)))
+            old.clear()
+            del old
+        if True:
             Np = Fc * h * w
             ws = {
                 "corr2": self._rows_buf(2 * Np, 324),
@@ -152,7 +176,19 @@ class MOFEngine:
                 "logits": torch.empty((h * w, h * w), dtype=torch.float32, device=self.dev),
                 "mask": self._rows_buf(Np, 576, torch.float32),
             }
-            self._ws = {key: ws}      # one shape at a time (volumes dominate memory)
+            if self.tiled and self.dev.type == "cuda":
+                # pyramids and the volume workspace live here, so the eager warm-up and the captured graph use the same
+                # memory (not one copy in the caching allocator and another in the graph's private pool)
+                ws["fpyr"] = self.ops.tiled_pyramid_alloc(Fc, h, w, self.dev)
+                ws["bpyr"] = self.ops.tiled_pyramid_alloc(Fc, h, w, self.dev)
+                ws["vol_ws"] = self.ops.tiled_volume_workspace(Fc, 256, h, w, self.dev)
+            # split-K partial sums of the aggregate, sized once for the worst split of this shape: graphs captured earlier
+            # keep the raw pointer, so the buffer may never be replaced afterwards
+            P = h * w
+            s_max = max([self._splits(P, k * P) for k in range(1, 4)] + [1])
+            for f in range(Fc):
+                ws[f"partial{f}"] = torch.empty(s_max * P * 128, dtype=torch.float32, device=self.dev)
+            self._ws[key] = ws
         return ws
 
     @staticmethod
@@ -198,11 +234,11 @@ class MOFEngine:
         S equal multiples of 64 until most SMs have a CTA (measured at C1: S = 2, 5, 10 -> 29, 30, 35 us against 40 us unsplit;
         the partial sums cost S x 3.6 MB per frame).  1 = not worth it / not divisible."""
         m_tiles = (M + 127) // 128
-        if K % 64 or m_tiles >= 148:
+        if K % 64 or m_tiles >= _sm_count():
             return 1
         nkb = K // 64
         for S in range(2, nkb + 1):
-            if nkb % S == 0 and K // S >= 512 and m_tiles * S >= 100:
+            if nkb % S == 0 and K // S >= 512 and m_tiles * S >= 100 * _sm_count() // 148:
                 return S
         return 1
 
@@ -216,6 +252,8 @@ class MOFEngine:
         key = f"partial{slot}"
         part = ws.get(key)
         if part is None or part.numel() < S * M * out.shape[1]:
+            if ws.get("graph") is not None or ws.get("graphs"):
+                raise RuntimeError("split-K partial buffer too small after graph capture (captured graphs hold its address)")
             part = ws[key] = torch.empty(S * M * out.shape[1], dtype=torch.float32, device=self.dev)
         return self.ops.gemm_splitk(attn, vT, out, S, part, res=res, alpha=self.gamma)
 
@@ -244,10 +282,20 @@ class MOFEngine:
             o.gemm(t2[rsl], W.w2b[wsl], out, bias=W.b2b[wsl].contiguous(), act=act, weights=True)
 
     # ------------------------------------------------------------------ pieces
+    def _guard(self):
+        """Every launch below goes to the current stream of the CURRENT device: make that the engine's device (the
+        reference wrappers accept any `device` without the caller calling torch.cuda.set_device first)."""
+        import contextlib
+        return torch.cuda.device(self.dev) if self.dev.type == "cuda" else contextlib.nullcontext()
+
     @torch.no_grad()
     def encode(self, images):
         """images [1, T, 3, H, W] (raw caller values) -> fmaps [T,256,h,w], net, inp [T-2,128,h,w].
         network.py:144-170 (the 2*(x/255)-1 normalisation stays inside)."""
+        with self._guard():
+            return self._encode(images)
+
+    def _encode(self, images):
         B, T, _, H, W = images.shape
         x = 2 * (images.float() / 255.0) - 1.0
         self._fork_side()                                   # the context encoder runs beside the feature encoder
@@ -260,13 +308,26 @@ class MOFEngine:
         net, inp = torch.split(cnet, [128, 128], dim=1)
         return fmaps, torch.tanh(net).contiguous(), torch.relu(inp).contiguous()
 
-    def build_pyramids(self, fmaps):
+    @torch.no_grad()
+    def encode_frames(self, frames, context=False):
+        """Per-frame halves of `encode` for the feature cache (fnet and cnet are per-image functions, network.py:150,161):
+        frames [n, 3, H, W] (raw caller values, already padded) -> fmaps [n, 256, h, w] (context=False) or the context
+        encoder's (tanh(net), relu(inp)) [n, 128, h, w] each (context=True)."""
+        with self._guard():
+            x = 2 * (frames.float() / 255.0) - 1.0
+            if not context:
+                return self.fnet(x).float()
+            net, inp = torch.split(self.cnet(x), [128, 128], dim=1)
+            return torch.tanh(net).float().contiguous(), torch.relu(inp).float().contiguous()
+
+    def build_pyramids(self, fmaps, ws=None):
         """Forward (frames 1..T-2 vs 2..T-1) and backward (vs 0..T-3) pyramids, network.py:157-158."""
         T = fmaps.shape[0]
         c = fmaps[1:T - 1].contiguous()
         if self.tiled:
-            return (self.ops.corr_volume_pyramid_tiled(c, fmaps[2:T].contiguous()),
-                    self.ops.corr_volume_pyramid_tiled(c, fmaps[0:T - 2].contiguous()))
+            ws = ws or {}
+            return (self.ops.corr_volume_pyramid_tiled(c, fmaps[2:T].contiguous(), ws.get("vol_ws"), out=ws.get("fpyr")),
+                    self.ops.corr_volume_pyramid_tiled(c, fmaps[0:T - 2].contiguous(), ws.get("vol_ws"), out=ws.get("bpyr")))
         fw = self.ops.corr_volume_pyramid(c, fmaps[2:T].contiguous(), CORR_LEVELS, self.dt)
         bw = self.ops.corr_volume_pyramid(c, fmaps[0:T - 2].contiguous(), CORR_LEVELS, self.dt)
         return fw, bw
@@ -355,11 +416,11 @@ class MOFEngine:
         d = direction if self.arch == "mof" else 1 - direction
         return slice(576 * d, 576 * (d + 1))
 
-    def _iterations_body(self, ws, fmaps, net, inp, Fc, h, w):
+    def _iterations_body(self, ws, fmaps, net, inp, Fc, h, w, iters=None):
         """pyramids, attention, `iters` update steps.  Leaves net in x512[:, 0:128]; returns the coords."""
         o = self.ops
         P = h * w
-        fpyr, bpyr = self.build_pyramids(fmaps)
+        fpyr, bpyr = self.build_pyramids(fmaps, ws)
         x512 = ws["x512"]
         o.nchw_to_rows(net, x512[:, 0:128])
         o.nchw_to_rows(inp, x512[:, 128:256])
@@ -368,7 +429,7 @@ class MOFEngine:
         self.attention(ws, Fc, P)
         fc = o.coords_grid(Fc, h, w, self.dev)
         bc = o.coords_grid(Fc, h, w, self.dev)
-        for _ in range(self.iters):
+        for _ in range(self.iters if iters is None else iters):
             self.update_step(ws, fpyr, bpyr, fc, bc, Fc, h, w)
         return fc, bc
 
@@ -383,8 +444,8 @@ class MOFEngine:
             static = [torch.empty_like(t) for t in (fmaps, net, inp)]
             for s_, t in zip(static, (fmaps, net, inp)):
                 s_.copy_(t)
-            self._iterations_body(ws, *static, Fc, h, w)            # eager warm-up: one-time kernel attributes
-            torch.cuda.synchronize()
+            self._iterations_body(ws, *static, Fc, h, w, iters=1)   # eager warm-up (one iteration reaches every kernel): module
+            torch.cuda.synchronize(self.dev)                        # loading and one-time attributes cannot happen under capture
             graph = torch.cuda.CUDAGraph()
             n0 = _lib.launch_count()
             with torch.cuda.graph(graph):
@@ -403,6 +464,10 @@ class MOFEngine:
         """fmaps [T,256,h,w], net/inp [T-2,128,h,w] (fp32, CUDA).
         select=None  -> all flows [1, 2(T-2), 2, 8h, 8w] (forward flows then backward), network.py:210-215
         select=index -> only that flow [2, out_h, out_w]; crop=(top, left, out_h, out_w) fuses the unpad."""
+        with self._guard():
+            return self._refine(fmaps, net, inp, select, crop, out)
+
+    def _refine(self, fmaps, net, inp, select, crop, out):
         o = self.ops
         T, _, h, w = fmaps.shape
         Fc, P = T - 2, h * w

@@ -5,6 +5,7 @@ streams only; every function launches libvfml kernels on the current CUDA stream
 [n_rows, pitch] buffer are fine); their row stride is the pitch handed to the kernels.
 """
 import ctypes as C
+import functools
 
 import torch
 
@@ -199,8 +200,17 @@ def corr_tile_pyramid(vol0, h, w):
     return TiledPyramid(levels, rows // (h * w), h, w)
 
 
-def corr_volume_pyramid_tiled(fmap1, fmap2, workspace=None):
-    """fmaps [n, C, h, w] fp32 -> TiledPyramid (tcgen05 GEMM + fused pool/tile pass)."""
+def tiled_pyramid_alloc(n, h, w, device):
+    """Uninitialised TiledPyramid for n frames (to be filled by corr_volume_pyramid_tiled(..., out=))."""
+    return TiledPyramid(_tiled_levels(n * h * w, h, w, device), n, h, w)
+
+
+def tiled_volume_workspace(n, Cc, h, w, device):
+    return torch.empty(max(_lib.load().vfml_corr_volume_tiled_workspace(n, Cc, h, w), 1), dtype=torch.uint8, device=device)
+
+
+def corr_volume_pyramid_tiled(fmap1, fmap2, workspace=None, out=None):
+    """fmaps [n, C, h, w] fp32 -> TiledPyramid (tcgen05 GEMM + fused pool/tile pass); `out`: a TiledPyramid to fill."""
     _cuda(fmap1, fmap2)
     _f32c(fmap1, "fmap1"); _f32c(fmap2, "fmap2")
     if fmap1.shape != fmap2.shape or fmap1.dim() != 4:
@@ -209,14 +219,16 @@ def corr_volume_pyramid_tiled(fmap1, fmap2, workspace=None):
     if h < 8 or w < 8:
         raise ValueError(f"corr_volume_pyramid_tiled: {h}x{w} is too small for 4 levels")
     lib = _lib.load()
-    levels = _tiled_levels(n * h * w, h, w, fmap1.device)
+    if out is not None and (out.n, out.h, out.w) != (n, h, w):
+        raise ValueError("corr_volume_pyramid_tiled: `out` was allocated for another shape")
+    levels = out.levels if out is not None else _tiled_levels(n * h * w, h, w, fmap1.device)
     arr = (C.c_void_p * 4)(*[l.data_ptr() for l in levels])
     ws_bytes = lib.vfml_corr_volume_tiled_workspace(n, Cc, h, w)
     if workspace is None or workspace.numel() < ws_bytes:
         workspace = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=fmap1.device)
     _lib.check(lib.vfml_corr_volume_pyramid_tiled(_p(fmap1), _p(fmap2), n, Cc, h, w, arr, 4, _p(workspace), workspace.numel(),
                                                   _stream()), "corr_volume_pyramid_tiled")
-    return TiledPyramid(levels, n, h, w)
+    return out if out is not None else TiledPyramid(levels, n, h, w)
 
 
 def corr_lookup_tiled(pyr_a, pyr_b, coords_a, coords_b, out_a, out_b, math_f32=False):
@@ -610,3 +622,40 @@ def im2col3x3(x, out, n_img, h, w):
     _lib.check(_lib.load().vfml_im2col3x3(_p(x), _p(out), n_img, h, w, Cc, x.stride(0), out.stride(0), _dt(x), _stream()),
                "im2col3x3")
     return out
+
+
+# ------------------------------------------------------------------ device guard
+def _first_cuda_device(args):
+    for a in args:
+        if isinstance(a, torch.Tensor):
+            if a.is_cuda:
+                return a.device
+        elif isinstance(a, TiledPyramid):
+            return a.levels[0].device
+        elif isinstance(a, torch.device) and a.type == "cuda":
+            return a
+        elif isinstance(a, str) and a.startswith("cuda"):
+            return torch.device(a)
+        elif isinstance(a, (list, tuple)) and a and isinstance(a[0], torch.Tensor) and a[0].is_cuda:
+            return a[0].device
+    return None
+
+
+def _on_tensor_device(fn):
+    """Kernels are launched on the current stream of the CURRENT device; run `fn` with the tensors' device current, so
+    that a processor built for 'cuda:1' works without the caller calling torch.cuda.set_device first."""
+    @functools.wraps(fn)
+    def wrapper(*args, **kw):
+        dev = _first_cuda_device(args) or _first_cuda_device(tuple(kw.values()))
+        if dev is None or dev.index is None or dev.index == torch.cuda.current_device():
+            return fn(*args, **kw)
+        with torch.cuda.device(dev):
+            return fn(*args, **kw)
+    return wrapper
+
+
+for _name, _fn in list(globals().items()):
+    if callable(_fn) and getattr(_fn, "__module__", None) == __name__ and not _name.startswith("_") \
+            and _name not in ("pyramid_shapes", "corr_lookup_perm", "TiledPyramid"):
+        globals()[_name] = _on_tensor_device(_fn)
+del _name, _fn

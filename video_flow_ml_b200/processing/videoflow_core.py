@@ -1,5 +1,6 @@
 """VideoFlowCore on libvfml kernels.  Mirrors processing/videoflow_core.py:33-242 of the reference:
 same constructor, methods, checkpoint naming, return values and exceptions."""
+import collections
 import os
 
 import torch
@@ -39,6 +40,11 @@ class VideoFlowCore:
             raise ValueError(f"precision must be one of {sorted(_PRECISIONS)}, got {self.precision}")
         self.model = None
         self.cfg = None
+        # per-frame feature cache: fnet / cnet are per-image functions (network.py:150,161), and sliding
+        # windows share T-1 of their T frames, so a steady-state window encodes ONE new frame instead of T + (T-2)
+        self.feature_cache_frames = int(os.environ.get("VFML_FEATURE_CACHE", "96"))
+        self._feat = collections.OrderedDict()        # key -> {"fmap": [256,h,w], "ctx": (net, inp) or None}
+        self.cache_stats = {"fnet_runs": 0, "cnet_runs": 0, "fnet_hits": 0, "cnet_hits": 0}
 
     # ------------------------------------------------------------------ loading
     def _model_path(self):
@@ -78,6 +84,7 @@ class VideoFlowCore:
         self.cfg = self._make_cfg(model_path)
         if self.architecture == 'bof' and iters == 32:
             iters = 12            # VideoFlow/configs/things.py:31 (BOFNet.decoder_depth)
+        self._feat.clear()
         self.model = MOFEngine(state_dict, self.device, _PRECISIONS[self.precision], iters=iters,
                                encoder_dtype=_PRECISIONS[self.precision] if self.precision == "fp16" else None,
                                arch=self.architecture)
@@ -112,6 +119,72 @@ class VideoFlowCore:
         with torch.no_grad():
             fmaps, net, inp = self.model.encode(x)
             return self.model.refine(fmaps, net, inp, select=Tn - 2, crop=(t, l, H, W), out=out)
+
+    def compute_flow_from_frames(self, frames, keys, out=None):
+        """Same result as compute_flow_from_tensor(stack(frames)[None]) for a window given frame by frame, with the
+        encoders' outputs cached per frame.  frames: T tensors [3, H, W] on the device (values as the caller would stack
+        them), or callables returning one (evaluated only for frames whose features are not cached, so a cached frame
+        is not even uploaded); keys: T hashable frame identities (None = do not cache that frame)."""
+        if self.model is None:
+            raise RuntimeError("VideoFlow model not loaded. Call load_model() first.")
+        Tn = len(frames)
+        if Tn < 3 or len(keys) != Tn:
+            raise ValueError("compute_flow_from_frames needs >= 3 frames and one key per frame")
+        centre = range(1, Tn - 1)
+        ent = [self._feat.get(k) if k is not None else None for k in keys]
+        need_f = [i for i in range(Tn) if ent[i] is None]
+        need_c = [i for i in centre if ent[i] is None or ent[i]["ctx"] is None]
+        # repeated frames of a padded window (clip start / end) are encoded once
+        first = {}
+        for i in sorted(set(need_f) | set(need_c)):
+            first.setdefault(keys[i] if keys[i] is not None else ("#", i), i)
+        loaded = {}
+
+        def tensor(i):
+            j = first[keys[i] if keys[i] is not None else ("#", i)]
+            if j not in loaded:
+                t = frames[j]() if callable(frames[j]) else frames[j]
+                H, W = t.shape[-2:]
+                l, r, tp, b = pad_amounts(H, W)
+                t = t[None]
+                if l or r or tp or b:
+                    t = torch.nn.functional.pad(t, [l, r, tp, b], mode='replicate')
+                loaded[j] = (t, H, W)
+            return loaded[j]
+        uniq_f = sorted({first[keys[i] if keys[i] is not None else ("#", i)] for i in need_f})
+        uniq_c = sorted({first[keys[i] if keys[i] is not None else ("#", i)] for i in need_c})
+        with torch.no_grad():
+            new = {}
+            if uniq_f:
+                fm = self.model.encode_frames(torch.cat([tensor(j)[0] for j in uniq_f]))
+                for n, j in enumerate(uniq_f):
+                    new[j] = {"fmap": fm[n], "ctx": None, "hw": tensor(j)[1:]}
+                self.cache_stats["fnet_runs"] += len(uniq_f)
+            if uniq_c:
+                net, inp = self.model.encode_frames(torch.cat([tensor(j)[0] for j in uniq_c]), context=True)
+                for n, j in enumerate(uniq_c):
+                    e = new.get(j) or ent[j]
+                    e["ctx"] = (net[n], inp[n])
+                self.cache_stats["cnet_runs"] += len(uniq_c)
+            self.cache_stats["fnet_hits"] += Tn - len(need_f)
+            self.cache_stats["cnet_hits"] += len(centre) - len(need_c)
+            for i in range(Tn):
+                if ent[i] is None:
+                    ent[i] = new[first[keys[i] if keys[i] is not None else ("#", i)]]
+                if keys[i] is not None and self.feature_cache_frames > 0:
+                    self._feat[keys[i]] = ent[i]
+                    self._feat.move_to_end(keys[i])
+            while len(self._feat) > self.feature_cache_frames:
+                self._feat.popitem(last=False)
+            H, W = ent[0]["hw"]
+            l, r, tp, b = pad_amounts(H, W)
+            fmaps = torch.stack([e["fmap"] for e in ent])
+            net = torch.stack([ent[i]["ctx"][0] for i in centre])
+            inp = torch.stack([ent[i]["ctx"][1] for i in centre])
+            return self.model.refine(fmaps, net, inp, select=Tn - 2, crop=(tp, l, H, W), out=out)
+
+    def clear_feature_cache(self):
+        self._feat.clear()
 
     def is_model_loaded(self):
         return self.model is not None

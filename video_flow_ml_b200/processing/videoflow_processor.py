@@ -1,5 +1,7 @@
 """VideoFlowProcessor on libvfml kernels.  Mirrors processing/videoflow_processor.py:20-361 of the
 reference (window choice, tile grid, progress-bar calls, validation, return types)."""
+import collections
+
 import numpy as np
 import torch
 
@@ -25,6 +27,11 @@ class VideoFlowProcessor:
         self.architecture = architecture
         self.variant = variant
         self.core = VideoFlowCore(device, fast_mode, dataset, architecture, variant, precision=precision)
+        # sliding windows over one clip share T-1 frames: their uploads and encoder outputs are cached by frame identity
+        # (array address, layout and a strided content sample).  set_feature_cache(False) restores one self-contained
+        # computation per call, for callers that rewrite frame arrays in place between calls.
+        self.feature_cache = True
+        self._dev_frames = collections.OrderedDict()      # frame key -> device tensor [H, W, 3]
 
     def load_model(self):
         model_path = self.core.load_model()
@@ -89,6 +96,67 @@ class VideoFlowProcessor:
             np.copyto(dst[i], f)
         return st[self._stage_i]
 
+    # ------------------------------------------------------------------ per-frame cache
+    def set_feature_cache(self, enabled):
+        self.feature_cache = bool(enabled)
+        if not enabled:
+            self._dev_frames.clear()
+            self.core.clear_feature_cache()
+
+    @staticmethod
+    def _frame_key(f):
+        """Identity of a frame array: address, layout, and 4 KB of strided content (an in-place edit of the array is
+        noticed unless it misses every sampled byte; callers that do that should disable the cache)."""
+        flat = f.reshape(-1).view(np.uint8) if f.flags.c_contiguous else np.ascontiguousarray(f).reshape(-1).view(np.uint8)
+        step = max(1, flat.size // 4096)
+        return (f.__array_interface__['data'][0], f.shape, f.dtype.str, f.strides, hash(flat[::step].tobytes()))
+
+    def _device_frame(self, f, key):
+        """The frame on the device ([H, W, 3], uint8 or float32), uploaded once per key through pinned staging."""
+        t = self._dev_frames.get(key)
+        if t is not None:
+            self._dev_frames.move_to_end(key)
+            return t
+        if f.dtype == np.uint8:
+            ring = getattr(self, "_pin_ring", None)
+            if ring is None or tuple(ring[0][0].shape) != f.shape:
+                pin = str(self.device).startswith("cuda") and torch.cuda.is_available()
+                ring = self._pin_ring = [(torch.empty(f.shape, dtype=torch.uint8, pin_memory=pin),
+                                          torch.cuda.Event() if pin else _NoEvent()) for _ in range(8)]
+                self._pin_i = 0
+            self._pin_i = (self._pin_i + 1) % len(ring)
+            buf, ev = ring[self._pin_i]
+            ev.synchronize()                   # the copy that last read this staging buffer has finished
+            np.copyto(buf.numpy(), f)
+            t = buf.to(self.device, non_blocking=True)
+            ev.record()
+        else:
+            t = torch.from_numpy(np.ascontiguousarray(f, dtype=np.float32)).to(self.device)
+        self._dev_frames[key] = t
+        while len(self._dev_frames) > 2 * max(self.sequence_length, 5):
+            self._dev_frames.popitem(last=False)
+        return t
+
+    @staticmethod
+    def _chw(t, rect=None):
+        """Device frame [H, W, 3] (optionally a tile of it) -> [3, h, w] fp32 as prepare_frame_sequence would make it."""
+        if rect is not None:
+            x, y, w, h = rect
+            t = t[y:y + h, x:x + w]
+        t = t.permute(2, 0, 1)
+        return t.float() / 255.0 if t.dtype == torch.uint8 else t.float()
+
+    def _cached_window(self, frames, frame_idx):
+        """(frames on demand, keys) of the window for VideoFlowCore.compute_flow_from_frames, or None when the frames
+        are not plain same-shape arrays (then the uncached tensor path is used)."""
+        ids = self.window_indices(len(frames), frame_idx)
+        seq = [frames[i] for i in ids]
+        if not (self.feature_cache and self.sequence_length >= 3 and all(isinstance(f, np.ndarray) and f.ndim == 3 for f in seq)
+                and len({(f.shape, f.dtype) for f in seq}) == 1):
+            return None
+        keys = [self._frame_key(f) for f in seq]
+        return seq, keys
+
     # ------------------------------------------------------------------ inference
     def compute_optical_flow(self, frames, frame_idx, return_device=False):
         """-> np.float32 [H, W, 2] like the reference (:164-187).  return_device=True keeps the [H, W, 2] flow on the GPU
@@ -96,7 +164,13 @@ class VideoFlowProcessor:
         effects.TAAProcessor accept CUDA tensors, so flow -> encode -> TAA needs no host round trip."""
         if not self.core.is_model_loaded():
             raise RuntimeError("Model not loaded. Call load_model() first.")
-        flow = self.core.compute_flow_from_tensor(self.prepare_frame_sequence(frames, frame_idx))
+        cw = self._cached_window(frames, frame_idx)
+        if cw is not None:
+            seq, keys = cw
+            lazy = [(lambda f=f, k=k: self._chw(self._device_frame(f, k))) for f, k in zip(seq, keys)]
+            flow = self.core.compute_flow_from_frames(lazy, keys)
+        else:
+            flow = self.core.compute_flow_from_tensor(self.prepare_frame_sequence(frames, frame_idx))
         if return_device:
             return flow.permute(1, 2, 0)
         return flow.permute(1, 2, 0).cpu().numpy()
@@ -132,7 +206,8 @@ class VideoFlowProcessor:
         height, width = frames[frame_idx].shape[:2]
         _, _, _, _, tiles_info = self.calculate_tile_grid(width, height)
         full = torch.zeros((2, height, width), dtype=torch.float32, device=self.device)
-        window = self.prepare_frame_sequence(frames, frame_idx)
+        cw = self._cached_window(frames, frame_idx)
+        window = self.prepare_frame_sequence(frames, frame_idx) if cw is None else None
         for i, ti in enumerate(tiles_info):
             if overall_pbar is not None:
                 overall_pbar.set_description(f"Tile {i+1}/{len(tiles_info)} ({ti['width']}x{ti['height']})")
@@ -140,8 +215,14 @@ class VideoFlowProcessor:
                 tile_pbar.set_description("Running VideoFlow")
                 tile_pbar.reset()
             x, y, w, h = ti['x'], ti['y'], ti['width'], ti['height']
-            tile = window[..., y:y + h, x:x + w].contiguous()
-            self.core.compute_flow_from_tensor(tile, out=full[:, y:y + h, x:x + w])
+            if cw is not None:          # per-(frame, tile) encoder cache; the frame itself is uploaded once for all its tiles
+                seq, keys = cw
+                rect = (x, y, w, h)
+                lazy = [(lambda f=f, k=k: self._chw(self._device_frame(f, k), rect)) for f, k in zip(seq, keys)]
+                self.core.compute_flow_from_frames(lazy, [k + rect for k in keys], out=full[:, y:y + h, x:x + w])
+            else:
+                tile = window[..., y:y + h, x:x + w].contiguous()
+                self.core.compute_flow_from_tensor(tile, out=full[:, y:y + h, x:x + w])
             if tile_pbar is not None:
                 tile_pbar.set_description("Completed")
                 tile_pbar.update(4)
