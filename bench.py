@@ -1,21 +1,27 @@
 #!/usr/bin/env python
-"""Benchmark of the MOF optical-flow hot path (BASELINE.json: MOF seq-5 436x1024 flow frames/s).
+"""Benchmark of the optical-flow hot path (BASELINE.json: MOF seq-5 436x1024 flow frames/s at 1/2/4/8 B200).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--precision fp32|fp16] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--config C1|C2|C3|C4|C5] [--precision fp16|fp32] [--impl reference]
 
-A "step" is one window (= one output flow frame = one call of compute_optical_flow): encoders on the
-window's frames, two correlation pyramids, GMA attention, 32 update iterations, mask head + convex
-upsampling of the consumed flow.  Synthetic clip (seed 1234) and seeded synthetic weights: there are
-no datasets or checkpoints offline.
+A "step" is one output flow frame (= one window = one call of compute_optical_flow): encoders on the window's NEW frame
+(the other T-1 frames' features come from the per-frame cache, exactly as in a real sliding pass over a clip), the
+correlation pyramids, GMA attention, the update iterations, mask head + convex upsampling of the consumed flow.
+Synthetic clip of distinct frames (no window ever recurs, so nothing but genuinely shared frames is cached) and seeded
+synthetic weights: there are no datasets or checkpoints offline.
 
-value : windows/s with the window tensor already resident in HBM (device timed, CUDA events).
-e2e   : windows/s through VideoFlowProcessor.compute_optical_flow with HOST numpy frames
-        (u8 upload of the window and fp32 download of the flow inside the timed region).
-roofline : the correlation lookup kernel (HBM bound), algorithmic bytes / CUDA-event time.
-cpu_baseline : the oracle (CPU port of the reference) on this box's host cores, bounded sample.
+value    : frames/s with the clip's frames already resident in HBM (device timed, CUDA events, max over ranks).
+e2e      : the same job through VideoFlowProcessor.compute_optical_flow with HOST numpy frames (upload of the new frame
+           from pinned memory and download of the fp32 flow inside the timed region).
+value_uncached : the round-1 measurement (every window self-contained: T + (T-2) encoder passes), for continuity.
+roofline : the kernel that dominates the step by time (gemm_tc_kernel); roofline_lookup: the HBM-bound lookup.
+cpu_baseline / --impl reference : the oracle (CPU restatement of the reference, pinned to it by tests/golden) on the
+           box's host cores; full windows are timed, nothing is extrapolated unless the line says so.
+torch_gpu_baseline : the same oracle's torch ops on this GPU (fp32 and fp16 autocast as the reference ships it):
+           the stand-in for BASELINE.md's B-GPU-ref, the denominator of the north star's ">= 25x" target.
 
-N > 1 (torchrun): windows are sharded over ranks, no data-path collective; the finished flows are
-gathered to rank 0 with NCCL inside the timed region; value = all ranks' windows / max-rank time.
+N > 1 (torchrun): ONE clip, its frames sharded over the ranks in contiguous ranges (sharding.shard_range; each rank
+re-encodes its floor(T/2)-frame halo), no data-path collective; the finished flows are gathered to rank 0 with NCCL
+inside the timed region.  C1 / C2 / C4 keep per-GPU work fixed ("weak"), C3 / C5 fix the total ("strong").
 """
 import argparse
 import json
@@ -29,17 +35,36 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
 
-H, W, T, ITERS, CLIP = 436, 1024, 5, 32, 8
-WORKLOAD = "MOF_sintel T=5, 8 synthetic 436x1024 frames, 32 iterations (BASELINE.json configs[0]/[1] shape C1)"
+CONFIGS = {
+    # name: BASELINE.json configs[] entry it measures
+    "C1": dict(arch="mof", T=5, H=436, W=1024, iters=32, tile=False, scaling="weak", metric="MOF seq5 436x1024 flow frames/s",
+               workload="MOF_sintel T=5, synthetic 436x1024 clip, 32 iterations (BASELINE.json configs[0]/[1])"),
+    "C2": dict(arch="bof", T=3, H=1080, W=1920, iters=12, tile=True, scaling="weak", metric="BOF 1080p tile-mode flow frames/s",
+               workload="BOF_things T=3, synthetic 1080p clip, --tile mode (1280x1080 + 640x1080 tiles), 12 iterations (configs[2])"),
+    "C3": dict(arch="mof", T=9, H=376, W=1242, iters=32, tile=False, scaling="strong", total=64, metric="MOF seq9 376x1242 flow frames/s",
+               workload="MOF_kitti T=9, 64 synthetic 376x1242 frames sharded over the GPUs, 32 iterations (configs[3])"),
+    "C4": dict(arch="memflow", T=2, H=436, W=1024, iters=15, tile=False, scaling="weak", metric="MemFlow 436x1024 streaming flow frames/s",
+               workload="MemFlowNet_sintel streaming memory-attention inference, synthetic 436x1024 clip, 15 iterations (configs[4])"),
+    "C5": dict(arch="mof", T=7, H=2160, W=3840, iters=32, tile=True, scaling="strong", total=16, post=True,
+               metric="MOF seq7 4K tile-mode + gamedev encode + TAA frames/s",
+               workload="MOF T=7, 16 synthetic 2160x3840 frames, tile mode (3x 1280x1280 + 3x 1280x880), gamedev encoding + flow TAA (configs[5])"),
+}
 
 
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
             p = json.load(f)
-        return float(p["hbm_gbs"]), "measured"
+        return float(p["hbm_gbs"]), float(p["bf16_tflops"]), "measured (MEASURED_PEAKS.json, burst figures: the kernels are timed alone)"
     except Exception:
-        return 6650.0, "fallback"
+        return 6650.0, 1600.0, "fallback (B200_PROFILING.md)"
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
 
 
 class ClockSampler(threading.Thread):
@@ -74,49 +99,413 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons, "samples": len(sm)}
 
 
-def cpu_port_times(n_iter=2):
-    """Oracle (CPU restatement of the reference) on the C1 window: returns (t_encode, t_setup, t_iter, cores)."""
+# ------------------------------------------------------------------------------------------ CPU oracle (reference arm)
+def _oracle_window_fn(cfg, device="cpu", amp=None):
+    """Returns run(iters) -> seconds: one full window of `cfg` through the oracle's restatement of the
+    reference (torch fp32 ops), from host uint8 frames to the returned flow."""
+    import numpy as np
     import torch
     import cases
-    from oracle import mof as omof
-    cores = os.cpu_count() or 1
+    T, H, W = cfg["T"], cfg["H"], cfg["W"]
+    frames = cases.sliding_clip(0, max(T, 3), H, W, seed=1234)
+    if cfg["arch"] == "memflow":
+        from oracle import memflow as omem
+        from oracle import mof as omof
+        sd = {k: v.to(device) for k, v in omem.memflow_synthetic_weights(0).items()}
+
+        def run(iters):
+            x = torch.stack([torch.from_numpy(f).permute(2, 0, 1).float() for f in frames[:3]])[None].to(device)
+            x = omof.pad_frames(2 * (x / 255.0) - 1.0)
+            core = omem.InferenceCore(sd, iters=iters)
+            with torch.no_grad():
+                core.step(x[:, 0:2])                  # fills the memory (not timed)
+                t0 = time.perf_counter()
+                core.step(x[:, 1:3])[1].float().cpu()
+            return time.perf_counter() - t0
+        return run
+    if cfg["arch"] == "bof":
+        from oracle import bof as ob
+        from oracle import mof as omof
+        sd = {k: v.to(device) for k, v in ob.bof_synthetic_weights(0).items()}
+        fwd = lambda win, iters: ob.core_compute_flow(win, sd, iters=iters)
+    else:
+        from oracle import mof as omof
+        sd = {k: v.to(device) for k, v in omof.mof_synthetic_weights(0, gain=1.0).items()}
+
+        def fwd(win, iters):
+            Hh, Ww = win.shape[-2:]
+            fm, net, inp = omof.mof_encode(omof.pad_frames(win), sd, amp=amp)
+            flows = omof.unpad(omof.mof_refine(fm, net, inp, sd, iters=iters, amp=amp), Hh, Ww)
+            return flows[0, flows.shape[1] // 2]
+
+    def run(iters):
+        t0 = time.perf_counter()
+        with torch.no_grad():
+            win = omof.frames_to_window(frames, T // 2, T).to(device)
+            if cfg["tile"]:
+                for ti in omof.tile_grid(W, H)[4]:
+                    out = fwd(win[..., ti["y"]:ti["y"] + ti["height"], ti["x"]:ti["x"] + ti["width"]].contiguous(), iters)
+            else:
+                out = fwd(win, iters)
+            out = out.float().cpu()
+            if device != "cpu":
+                torch.cuda.synchronize()
+        return time.perf_counter() - t0
+    return run
+
+
+def cpu_oracle_timing(cfg, budget_s, max_windows):
+    """Times FULL windows of the oracle on every host core until `budget_s` is used (at least one).  A 2-iteration probe
+    first estimates the window time; only if one full window would not fit the budget is the result extrapolated
+    (and flagged).  -> dict(value frames/s from the best window, samples, cores, extrapolated, ...)."""
+    import torch
+    cores = host_cores()
     torch.set_num_threads(cores)
-    sd = omof.mof_synthetic_weights(0)
-    frames = cases.synthetic_clip(T, H, W, seed=1234)
-    win = omof.pad_frames(omof.frames_to_window(frames, T // 2, T))
-    with torch.no_grad():
-        t0 = time.perf_counter()
-        fmaps, net, inp = omof.mof_encode(win, sd)
-        t_enc = time.perf_counter() - t0
-        t0 = time.perf_counter()
-        omof.mof_refine(fmaps, net, inp, sd, iters=1)
-        t1 = time.perf_counter() - t0
-        t0 = time.perf_counter()
-        omof.mof_refine(fmaps, net, inp, sd, iters=1 + n_iter)
-        t2 = time.perf_counter() - t0
-    t_iter = max((t2 - t1) / n_iter, 1e-9)
-    return t_enc, max(t1 - t_iter, 0.0), t_iter, cores
+    run = _oracle_window_fn(cfg)
+    iters = cfg["iters"]
+    t1 = run(1)                                   # also the warm-up (thread pool, allocator, oneDNN primitives)
+    t3 = run(3)
+    t_iter = max((t3 - t1) / 2.0, 1e-9)
+    est = max(t1 - t_iter, 0.0) + iters * t_iter
+    out = {"cores": cores, "kind": "port", "probe_s": {"iters_1": t1, "iters_3": t3}, "estimated_window_s": est}
+    if est > budget_s:
+        out.update(extrapolated=True, iters_timed=3, windows_timed=0, window_s=[est], value=1.0 / est,
+                   sample=f"oracle window at full size, measured at 1 and 3 update iterations and extrapolated linearly to {iters} "
+                          f"(one full window, ~{est:.0f} s, would exceed the {budget_s:.0f} s budget)")
+        return out
+    times, t_start = [], time.perf_counter()
+    while len(times) < max_windows and (not times or time.perf_counter() - t_start + est <= budget_s):
+        times.append(run(iters))
+    best = min(times)
+    out.update(extrapolated=False, iters_timed=iters, windows_timed=len(times), window_s=times, value=1.0 / best,
+               sample=f"{len(times)} full oracle window(s) at full size and all {iters} iterations (host frames -> flow), "
+                      f"{cores} threads; value = best window (min of {len(times)})")
+    return out
 
 
 def run_reference(args):
-    """--impl reference: the reference's own CPU algorithm (oracle port) on the host cores, all threads."""
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
+    """--impl reference: the reference's CPU algorithm (oracle port: /root/reference does not travel to the GPU box and
+    its Twins encoder needs the absent timm) on the host cores, all threads, FULL windows."""
+    if int(os.environ.get("RANK", "0")) != 0:
         return
-    vals = []
-    for _ in range(min(max(args.steps, 1), 3)):      # bounded: at most 3 full-size samples (~20 s each)
-        t_enc, t_setup, t_iter, cores = cpu_port_times(1)
-        vals.append(t_enc + t_setup + ITERS * t_iter)
-    t = sum(vals) / len(vals)
-    sample = ("per step: oracle MOF window 436x1024 T=5 at full size: encoders + 2 corr pyramids + attention + 2 measured "
-              "update iterations, extrapolated linearly to 32 iterations")
-    v = 1.0 / t
-    print(json.dumps({"impl": "reference", "metric": "MOF seq5 436x1024 flow frames/s", "value": v, "unit": "frames/s",
-                      "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000 * t,
-                      "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                      "config": {"workload": WORKLOAD},
-                      "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
-                      "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+    cfg = CONFIGS[args.config]
+    budget = float(os.environ.get("VFML_REF_BUDGET_S", "150"))
+    r = cpu_oracle_timing(cfg, budget, max(args.steps, 1))
+    if r["extrapolated"]:          # what was really run: the two probe samples
+        steps, ms = 2, 1000.0 * (r["probe_s"]["iters_1"] + r["probe_s"]["iters_3"]) / 2.0
+    else:
+        steps, ms = r["windows_timed"], 1000.0 * (sum(r["window_s"]) / len(r["window_s"]))
+    print(json.dumps({
+        "impl": "reference", "metric": cfg["metric"], "value": r["value"], "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": steps, "steps_requested": args.steps, "warmup": 1, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": cfg["scaling"], "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": cfg["workload"], "iterations": cfg["iters"], "config": args.config},
+        "extrapolated": r["extrapolated"], "iters_timed": r["iters_timed"], "ms_per_window": 1000.0 / r["value"],
+        "cpu_baseline": {"value": r["value"], "unit": "frames/s", "cores": r["cores"], "kind": "port", "sample": r["sample"],
+                         "window_s": r["window_s"], "probe_s": r["probe_s"]},
+        "e2e": {"value": r["value"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+# ------------------------------------------------------------------------------------------ torch-on-GPU baseline
+def torch_gpu_baseline(cfg, dev):
+    """BASELINE.md B-GPU-ref stand-in: the oracle's torch ops (the reference's own op sequence: matmul volume, avg_pool2d,
+    4x grid_sample lookups, conv2d / gelu / cat chains, einsum attention, unfold upsampling) on this GPU, host frames in,
+    flow out; fp32 and under fp16 autocast with fp32 volume + lookup as the reference ships it.
+    2 warm-up windows, median of 5."""
+    import torch
+    out = {}
+    for name, amp in (("fp32", None), ("fp16_autocast", torch.float16)):
+        try:
+            run = _oracle_window_fn(cfg, device=dev, amp=amp)
+            for _ in range(2):
+                run(cfg["iters"])
+            ts = sorted(run(cfg["iters"]) for _ in range(5))
+            out[name] = {"value": 1.0 / ts[2], "unit": "frames/s", "ms_per_window": 1000.0 * ts[2], "windows": 5}
+        except Exception as e:      # a baseline must not take the benchmark down
+            out[name] = {"error": f"{type(e).__name__}: {e}"[:200]}
+        torch.cuda.empty_cache()
+    out["note"] = ("oracle (pinned CPU restatement of the reference) executed with device='cuda': stock torch / cuDNN / cuBLAS "
+                   "kernels, Python loop, no graph capture -- the reference's own execution model on this GPU")
+    return out
+
+
+# ------------------------------------------------------------------------------------------ the B200 jobs
+class FlowJob:
+    """MOF / BOF over one clip through VideoFlowProcessor (tile mode when the config says so).  Frames of the clip are
+    generated per rank for its own range (+ halo); `resident=True` pre-uploads them so that the timed region sees no H2D."""
+
+    def __init__(self, cfg, dev, precision, iters, world, rank, steps):
+        import torch
+        import cases
+        from video_flow_ml_b200 import sharding
+        from video_flow_ml_b200.processing import VideoFlowProcessor
+        self.cfg, self.dev, self.world, self.rank, self.torch, self.cases, self.sharding = cfg, dev, world, rank, torch, cases, sharding
+        T = cfg["T"]
+        self.proc = VideoFlowProcessor(dev, sequence_length=T, tile_mode=cfg["tile"], architecture=cfg["arch"],
+                                       dataset="things" if cfg["arch"] == "bof" else "sintel", precision=precision)
+        if cfg["arch"] == "bof":
+            from oracle.bof import bof_synthetic_weights as weights        # seeded weight generators only (deterministic RNGs)
+            sd = weights(0)
+        else:
+            from oracle.mof import mof_synthetic_weights as weights
+            sd = weights(0)
+        self.proc.core.load_state_dict(sd, iters=iters)
+        self.H, self.W = cfg["H"], cfg["W"]
+        self.n_total = cfg["total"] if cfg["scaling"] == "strong" else world * steps
+        self.tiles = self.proc.calculate_tile_grid(self.W, self.H)[4] if cfg["tile"] else None
+        if cfg["tile"] and world > 1:
+            self.units, self.load = sharding.shard_tile_chunks(self.n_total, self.tiles, world, rank)
+            self.my_frames = sorted({f for _, a, b in self.units for f in range(a, b)})
+        else:
+            a, b = sharding.shard_range(self.n_total, world, rank)
+            self.units, self.my_frames = None, list(range(a, b))
+        self.proc.device_frame_capacity = len(self.my_frames) + 2 * T + 2
+        self.out = torch.zeros((max(len(self.my_frames), 1), 2, self.H, self.W), dtype=torch.float32, device=dev)
+        self.slot = {f: i for i, f in enumerate(self.my_frames)}
+        self.post = None
+        if cfg.get("post"):
+            from video_flow_ml_b200.effects import TAAProcessor
+            self.post = TAAProcessor(alpha=0.1, device=dev)
+
+    def clip(self, offset):
+        """Host frames of the whole clip index space as a lazy list: only this rank's range (+ halo) is generated."""
+        half = self.cfg["T"] // 2
+        need = sorted({j for f in self.my_frames for j in range(max(0, f - half), min(self.n_total, f + half + 1))})
+        frames = [None] * self.n_total
+        if need:
+            gen = self.cases.sliding_clip(offset + need[0], offset + need[-1] + 1, self.H, self.W, seed=1234)
+            for j in need:
+                frames[j] = gen[j - need[0]]
+        filler = next(f for f in frames if f is not None)
+        return [f if f is not None else filler for f in frames], need       # never-read slots hold a placeholder array
+
+    def upload(self, frames, need):
+        for j in need:
+            self.proc._device_frame(frames[j], self.proc._frame_key(frames[j]))
+
+    def run(self, frames, host_out):
+        """All of this rank's output frames; host_out=True is the public-API end-to-end call (numpy out)."""
+        p = self.proc
+        if self.units is None:
+            for f in self.my_frames:
+                if host_out:
+                    self.last_np = p.compute_optical_flow_tiled(frames, f)
+                else:
+                    self.out[self.slot[f]].copy_(p.compute_optical_flow_tiled(frames, f, return_device=True).permute(2, 0, 1))
+        else:
+            for ti, a, b in self.units:
+                for f in range(a, b):
+                    p.compute_tile_into(frames, f, self.tiles[ti], self.out[self.slot[f]])
+            if host_out:
+                self.last_np = self.out[-1].permute(1, 2, 0).cpu().numpy()
+
+    def gather(self):
+        """The job's only communication: finished flows to rank 0 (NCCL).  Contiguous shards: gather; tile chunks: the ranks'
+        disjoint tiles are summed into rank 0's full frames."""
+        import torch.distributed as dist
+        torch = self.torch
+        if self.world == 1:
+            return self.out
+        if self.units is None:
+            return self.sharding.gather_flows(self.out, self.n_total, self.world, self.rank, dst=0)
+        full = torch.zeros((self.n_total, 2, self.H, self.W), dtype=torch.float32, device=self.dev)
+        for f in self.my_frames:
+            full[f] = self.out[self.slot[f]]
+        dist.reduce(full, dst=0, op=dist.ReduceOp.SUM)
+        return full if self.rank == 0 else None
+
+    def post_pass(self, flows, frames_done):
+        """C5: gamedev encoding + flow TAA of every finished frame, device resident, on the rank that holds the clip."""
+        if self.post is None or flows is None:
+            return None
+        from video_flow_ml_b200.encoding import encode_flow
+        self.post.reset_history()
+        prev, res = None, None
+        for i in range(frames_done):
+            fl = flows[i].permute(1, 2, 0).contiguous()
+            enc = encode_flow(fl, self.W, self.H, "gamedev")
+            res = self.post.apply_taa(enc, prev, return_device=True)
+            prev = fl
+        return res
+
+    def launches(self):
+        from video_flow_ml_b200 import _lib
+        return _lib.launch_count() + self.proc.core.model.graph_launches
+
+    def bytes_per_step(self):
+        T = self.cfg["T"]
+        return self.H * self.W * 3, self.H * self.W * 2 * 4
+
+
+class MemFlowJob:
+    """MemFlow streaming (C4): one clip per rank (replicas: the memory makes frames of a clip sequential), InferenceCore.step
+    per frame pair with the memory engaged."""
+
+    def __init__(self, cfg, dev, precision, iters, world, rank, steps):
+        import torch
+        import cases
+        from oracle.memflow import memflow_synthetic_weights
+        from video_flow_ml_b200.processing import InferenceCore, MemFlowProcessor
+        self.cfg, self.dev, self.torch, self.cases, self.world, self.rank = cfg, dev, torch, cases, world, rank
+        self.proc = MemFlowProcessor(dev, precision=precision)
+        self.proc.core_engine.load_state_dict(memflow_synthetic_weights(0))
+        self.eng = self.proc.core_engine.model
+        self.eng.iters = iters
+        self.ic = InferenceCore(self.eng)
+        self.H, self.W = cfg["H"], cfg["W"]
+        self.n_total = world * steps
+        self.my_frames = list(range(steps))
+        self.out = torch.zeros((steps, 2, self.H, self.W), dtype=torch.float32, device=dev)
+        self.post = None
+        self.pad = [0, 0, 2, 2] if self.H % 8 else [0, 0, 0, 0]          # 436 -> 440 ('sintel' padding, top / bottom)
+        self.crop = (2, 0, self.H, self.W) if self.H % 8 else None
+        self.pin = torch.empty((self.H, self.W, 3), dtype=torch.uint8, pin_memory=True)
+
+    def clip(self, offset):
+        n = len(self.my_frames) + 1
+        return self.cases.sliding_clip(offset + 1000 * self.rank, offset + 1000 * self.rank + n, self.H, self.W, seed=1234), list(range(n))
+
+    def _norm(self, u8):
+        x = u8.permute(2, 0, 1).float()[None]
+        return self.torch.nn.functional.pad(2 * (x / 255.0) - 1.0, [0, 0] + self.pad[2:], mode="replicate")
+
+    def upload(self, frames, need):
+        self.dev_frames = [self._norm(self.torch.from_numpy(f).to(self.dev)) for f in frames]
+
+    def run(self, frames, host_out):
+        torch = self.torch
+        self.ic.clear_memory()
+        if host_out:
+            import numpy as np
+            prev = None
+            for t, f in enumerate(frames):
+                np.copyto(self.pin.numpy(), f)
+                cur = self._norm(self.pin.to(self.dev, non_blocking=True))
+                if prev is not None:
+                    _, up = self.ic.step(torch.stack([prev[0], cur[0]])[None], crop=self.crop)
+                    self.last_np = up[0].permute(1, 2, 0).cpu().numpy()
+                prev = cur
+        else:
+            for t in range(len(self.my_frames)):
+                _, up = self.ic.step(torch.stack([self.dev_frames[t][0], self.dev_frames[t + 1][0]])[None], crop=self.crop)
+                self.out[t].copy_(up[0])
+
+    def gather(self):
+        return self.out            # replicas: each rank keeps its own clip's flows
+
+    def post_pass(self, flows, n):
+        return None
+
+    def launches(self):
+        from video_flow_ml_b200 import _lib
+        return _lib.launch_count() + self.eng.graph_launches
+
+    def bytes_per_step(self):
+        return self.H * self.W * 3, self.H * self.W * 2 * 4
+
+
+# ------------------------------------------------------------------------------------------ kernel rooflines (C1 shapes)
+def _graph_time(torch, calls, reps):
+    """Average duration of one pass over `calls`, replayed from a CUDA graph (the engine's own launch mode), CUDA events
+    on the launching stream."""
+    for c in calls:
+        c()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(reps):
+            for c in calls:
+                c()
+    g.replay()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def roofline_gemm(torch, ops, eng, Fc, P, dev):
+    """The kernel that dominates the step by time: the 30 pointwise-convolution GEMMs of one update iteration on synthetic
+    activations of the real C1 shapes (fused epilogues included), timed alone."""
+    _, tpeak, src = peaks()
+    Np = Fc * P
+    rb = lambda n, c: torch.randn((n, (c + 15) // 16 * 16), device=dev).to(eng.dt)[:, :c]
+    calls, flops, abytes = [], 0.0, 0.0
+    for M, C, Co in ((2 * Np, 324, 128), (Np, 256, 192), (Np, 128, 64), (Np, 400, 172), (Np, 512, 128), (Np, 128, 4)):
+        hid = int(1.5 * C)
+        x, t1, x2, x3, o_ = rb(M, C), rb(M, hid), rb(M, C), rb(M, C), rb(M, Co)
+        w1a, w1b, wpw, w2a, w2b = rb(hid, C), rb(C, hid), rb(C, C), rb(hid, C), rb(Co, hid)
+        bh, bc, bo = (torch.randn(n, device=dev) for n in (hid, C, Co))
+        calls += [lambda x=x, w=w1a, o=t1, b=bh: ops.gemm(x, w, o, bias=b, act="gelu", weights=True),
+                  lambda x=t1, w=w1b, o=x2, b=bc, r=x: ops.gemm(x, w, o, bias=b, res=r, act="gelu", dw=(b, b), weights=True),
+                  lambda x=x3, w=wpw, o=x2, b=bc: ops.gemm(x, w, o, bias=b, res=x, act="gelu", weights=True),
+                  lambda x=x2, w=w2a, o=t1, b=bh: ops.gemm(x, w, o, bias=b, act="gelu", weights=True),
+                  lambda x=t1, w=w2b, o=o_, b=bo: ops.gemm(x, w, o, bias=b, weights=True)]
+        flops += 2.0 * M * (3 * hid * C + C * C + hid * Co)
+        abytes += 2.0 * M * (C + hid + hid + C + C + C + C + C + hid + hid + Co + C + C)      # activations read + written + residuals, fp16
+    g_ms = _graph_time(torch, calls, 4)
+    ach = flops / (g_ms * 1e-3) / 1e12
+    return {"kernel": "gemm_tc_kernel", "bound": "tensor", "achieved": ach, "peak": tpeak, "unit": "TFLOP/s", "frac": ach / tpeak,
+            "traffic": None, "traffic_source": "not captured in this run (ncu --set full summaries: profiles/)", "peak_source": src,
+            "launches": len(calls), "flops_per_iteration": flops, "algorithmic_bytes_per_iteration": abytes,
+            "us_per_iteration": g_ms * 1000.0,
+            "note": "the 30 pointwise-convolution GEMMs of one update iteration (SURVEY 8d: 114.4 GMAC minus the depthwise and "
+                    "mask-head terms) at C1 shapes; CUDA events over a graph replay of 4 iterations"}
+
+
+def roofline_lookup(torch, ops, eng, fmaps, Fc, hp, wp, dev):
+    hbm, _, src = peaks()
+    P = hp * wp
+    fpyr, bpyr = eng.build_pyramids(fmaps)
+    g = torch.Generator(device="cpu").manual_seed(7)
+    # 8 coordinate sets with uniformly random in-range targets: successive launches touch different texels of the
+    # 811 MB of tiled volumes (8 x ~100 MB of sectors >> 126 MB L2), so every launch streams from HBM
+    lo = torch.tensor([4.0, 4.0]).view(1, 2, 1, 1)
+    span = torch.tensor([wp - 9.0, hp - 9.0]).view(1, 2, 1, 1)
+    csets = [((lo + span * torch.rand((Fc, 2, hp, wp), generator=g)).to(dev).contiguous(),
+              (lo + span * torch.rand((Fc, 2, hp, wp), generator=g)).to(dev).contiguous()) for _ in range(8)]
+    out = torch.zeros((2 * Fc * P, 336), dtype=eng.dt, device=dev)[:, :324]
+    if eng.tiled:
+        kern = "corr_lookup_tiled_kernel"
+        calls = [lambda c=c: ops.corr_lookup_tiled(fpyr, bpyr, c[0], c[1], out[:Fc * P], out[Fc * P:], math_f32=eng.lookup_math_f32) for c in csets]
+    else:
+        kern = "corr_lookup_rows_kernel"
+        calls = [lambda c=c: ops.corr_lookup_pair(fpyr, bpyr, c[0], c[1], out[:Fc * P], out[Fc * P:]) for c in csets]
+    ms = _graph_time(torch, calls, 6) / len(calls)
+    es = 4 if eng.dt == torch.float32 else 2
+    alg = 2 * Fc * P * (4 * 100 * es + 8 + 324 * es)     # SURVEY 8(d): per pixel-direction 100 texels / level read + coords + 324 written
+    ach = alg / (ms * 1e-3) / 1e9
+    return {"kernel": kern, "bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm,
+            "traffic": 74438912 + 3937792 if eng.tiled else None,
+            "traffic_source": "ncu --set full capture of round 1 at commit 641d11c (profiles/r1_lookup_tiled_ncu_summary.txt, cold L2): "
+                              "dram__bytes_read.sum + dram__bytes_write.sum per launch; not re-measured in this run" if eng.tiled else None,
+            "peak_source": src, "algorithmic_bytes_per_launch": alg, "us_per_launch": ms * 1000.0}
+
+
+# ------------------------------------------------------------------------------------------ main
+def timed_job(torch, dist, job, world, frames, need, host_out):
+    """Barrier + sync on both sides, CUDA events on the launching stream, the gather inside; -> (ms, flows on rank 0)."""
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    if not host_out:
+        job.upload(frames, need)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    job.run(frames, host_out)
+    flows = job.gather()
+    res = job.post_pass(flows, job.n_total)
+    if host_out and res is not None:
+        job.last_np = res.cpu().numpy()
+    e1.record()
+    barrier()
+    wall = (time.perf_counter() - t0) * 1000.0
+    return (wall if host_out else e0.elapsed_time(e1)), flows
 
 
 def main():
@@ -125,21 +514,21 @@ def main():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
+    ap.add_argument("--config", default=os.environ.get("VFML_CONFIG", "C1"), choices=sorted(CONFIGS))
     ap.add_argument("--precision", default=os.environ.get("VFML_PRECISION", "fp16"))
-    ap.add_argument("--iters", type=int, default=ITERS)
+    ap.add_argument("--iters", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip rooflines, fp32 tier, torch-on-GPU and CPU baselines")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
 
-    import numpy as np
     import torch
     import torch.distributed as dist
-    import cases
-    from video_flow_ml_b200 import _lib, ops, sharding
-    from video_flow_ml_b200.processing import VideoFlowProcessor
-    from oracle.mof import mof_synthetic_weights      # seeded weight generator only (a deterministic RNG)
+    from video_flow_ml_b200 import ops
 
+    cfg = CONFIGS[args.config]
+    iters = args.iters or cfg["iters"]
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -147,187 +536,178 @@ def main():
     dev = f"cuda:{local}"
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device(dev))
-    warm = max(args.warmup, 3)
+    steps = max(args.steps, 1)
+    Job = MemFlowJob if cfg["arch"] == "memflow" else FlowJob
+    job = Job(cfg, dev, args.precision, iters, world, rank, steps)
 
-    proc = VideoFlowProcessor(dev, sequence_length=T, precision=args.precision)
-    proc.core.load_state_dict(mof_synthetic_weights(0), iters=args.iters)
-    # every rank owns its own shard of windows: a different clip per rank (weak scaling)
-    frames = cases.synthetic_clip(CLIP, H, W, seed=1234 + rank)
-    n_steps = args.steps
-    windows = [proc.prepare_frame_sequence(frames, i % CLIP) for i in range(CLIP)]
-    out = torch.empty((n_steps, 2, H, W), dtype=torch.float32, device=dev)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
+    # ---- warm-up: one full untimed pass over a DIFFERENT stretch of the clip (captures every graph, sets up NCCL)
+    wf, wneed = job.clip(offset=50000)
+    timed_job(torch, dist, job, world, wf, wneed, host_out=False)
+    n_warm = len(job.my_frames)
     # ---- device-resident arm ("value")
-    for i in range(warm):
-        proc.core.compute_flow_from_tensor(windows[i % CLIP], out=out[i % n_steps])
-    if world > 1:      # untimed: NCCL sets up its point-to-point channels lazily, on the first gather
-        sharding.gather_flows(out, world * n_steps, world, rank, dst=0)
-    barrier()
+    frames, need = job.clip(offset=0)
+    if hasattr(job, "proc") and hasattr(job.proc, "core"):
+        job.proc.core.cache_stats.update(fnet_runs=0, cnet_runs=0, fnet_hits=0, cnet_hits=0)
     sampler = ClockSampler(local)
     sampler.start()
-    n0 = _lib.launch_count() + proc.core.model.graph_launches
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e0.record()
-    for i in range(n_steps):
-        proc.core.compute_flow_from_tensor(windows[i % CLIP], out=out[i])
-    if world > 1:      # the only communication of the job: finished flows to rank 0 (NCCL over NVLink)
-        sharding.gather_flows(out, world * n_steps, world, rank, dst=0)
-    e1.record()
-    barrier()
-    launches = _lib.launch_count() + proc.core.model.graph_launches - n0     # direct launches + kernels replayed from the CUDA graph
-    ms = e0.elapsed_time(e1)
+    n0 = job.launches()
+    ms, _ = timed_job(torch, dist, job, world, frames, need, host_out=False)
+    launches = job.launches() - n0
     clocks = sampler.summary()
+    stats = dict(job.proc.core.cache_stats) if hasattr(job.proc, "core") else None
+    # ---- end-to-end arm: public API, host frames of another stretch (nothing of it is on the device or in any cache)
+    ef, eneed = job.clip(offset=100000)
+    e2e_ms, _ = timed_job(torch, dist, job, world, ef, eneed, host_out=True)
+    h2d, d2h = job.bytes_per_step()
+    if cfg.get("post"):
+        d2h = int(job.last_np.nbytes)
 
-    # ---- end-to-end arm through the public API with host frames
-    for i in range(2):
-        proc.compute_optical_flow(frames, i)
-    barrier()
-    t0 = time.perf_counter()
-    for i in range(n_steps):
-        flow_np = proc.compute_optical_flow(frames, i % CLIP)
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    h2d = T * H * W * 3                  # u8 window upload
-    d2h = int(flow_np.nbytes)
-
-    # ---- roofline of the lookup kernel, timed live with CUDA events on the launching stream
-    eng = proc.core.model
-    hp, wp = (H + 7) // 8 * 8 // 8, W // 8
-    Fc, P = T - 2, hp * wp
-    fmaps, net, inp = eng.encode(torch.nn.functional.pad(windows[0], [0, 0, 2, 2, 0, 0], mode="replicate"))
-    fpyr, bpyr = eng.build_pyramids(fmaps)
-    g = torch.Generator(device="cpu").manual_seed(7)
-    # 8 coordinate sets with uniformly random in-range targets: successive launches touch different texels of
-    # the 1.58 GB of volumes (8 x ~100 MB of sectors >> 126 MB L2), so every launch streams from HBM
-    n_sets = 8
-    lo = torch.tensor([4.0, 4.0]).view(1, 2, 1, 1)
-    span = torch.tensor([wp - 9.0, hp - 9.0]).view(1, 2, 1, 1)
-    csets = [((lo + span * torch.rand((Fc, 2, hp, wp), generator=g)).to(dev).contiguous(),
-              (lo + span * torch.rand((Fc, 2, hp, wp), generator=g)).to(dev).contiguous()) for _ in range(n_sets)]
-    lk_out = torch.zeros((2 * Fc * P, 328), dtype=eng.dt, device=dev)[:, :324]
-    reps = 48
-    if eng.tiled:
-        lk_kernel = "corr_lookup_tiled_kernel"
-        lookup = lambda cf, cb: ops.corr_lookup_tiled(fpyr, bpyr, cf, cb, lk_out[:Fc * P], lk_out[Fc * P:], math_f32=eng.lookup_math_f32)
-    else:
-        lk_kernel = "corr_lookup_rows_kernel"
-        lookup = lambda cf, cb: ops.corr_lookup_pair(fpyr, bpyr, cf, cb, lk_out[:Fc * P], lk_out[Fc * P:])
-    for i in range(n_sets):
-        lookup(*csets[i])
-    torch.cuda.synchronize()
-    # the launches are replayed from a CUDA graph (as in the engine) so that the ~20 us ctypes call is not what is timed
-    lk_graph = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(lk_graph):
-        for i in range(reps):
-            lookup(*csets[i % n_sets])
-    lk_graph.replay()
-    l0, l1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
-    l0.record()
-    lk_graph.replay()
-    l1.record()
-    torch.cuda.synchronize()
-    lk_ms = l0.elapsed_time(l1) / reps          # one launch = forward + backward lookup of one iteration
-    es = 4 if eng.dt == torch.float32 else 2
-    # DRAM bytes per launch of the roofline kernel on this workload, from the committed ncu --set full capture
-    NCU_TRAFFIC = {"corr_lookup_tiled_kernel": 74438912 + 3937792}
-    alg_bytes = 2 * Fc * P * (4 * 100 * es + 8 + 324 * es)   # per pixel-direction 100 texels/level read + coords + 324 written
-    peak, peak_kind = peaks()
-    achieved = alg_bytes / (lk_ms * 1e-3) / 1e9
-    del fpyr, bpyr
-
-    # ---- second roofline, for the kernel that dominates the step by time (gemm_tc_kernel, ~65 %): the 30 pointwise-
-    # convolution GEMMs of one update iteration on synthetic activations of the real shapes, replayed from a CUDA graph
-    gemm_roof = None
-    if eng.dt == torch.float16:
-        Np = Fc * P
-        rb = lambda n, c: torch.randn((n, (c + 7) // 8 * 8), device=dev).to(eng.dt)[:, :c]
-        calls, flops = [], 0.0
-        for M, C, Co in ((2 * Np, 324, 128), (Np, 256, 192), (Np, 128, 64), (Np, 400, 172), (Np, 512, 128), (Np, 128, 4)):
-            hid = int(1.5 * C)
-            x, t1, x2, x3, o_ = rb(M, C), rb(M, hid), rb(M, C), rb(M, C), rb(M, Co)
-            w1a, w1b, wpw, w2a, w2b = rb(hid, C), rb(C, hid), rb(C, C), rb(hid, C), rb(Co, hid)
-            bh, bc, bo = (torch.randn(n, device=dev) for n in (hid, C, Co))
-            calls += [lambda x=x, w=w1a, o=t1, b=bh: ops.gemm(x, w, o, bias=b, act="gelu", weights=True),
-                      lambda x=t1, w=w1b, o=x2, b=bc, r=x: ops.gemm(x, w, o, bias=b, res=r, act="gelu", dw=(b, b), weights=True),
-                      lambda x=x3, w=wpw, o=x2, b=bc: ops.gemm(x, w, o, bias=b, res=x, act="gelu", weights=True),
-                      lambda x=x2, w=w2a, o=t1, b=bh: ops.gemm(x, w, o, bias=b, act="gelu", weights=True),
-                      lambda x=t1, w=w2b, o=o_, b=bo: ops.gemm(x, w, o, bias=b, weights=True)]
-            flops += 2.0 * M * (3 * hid * C + C * C + hid * Co)      # ffn1.0, ffn1.2, ffn2.0 (hid x C each), pw (C x C), ffn2.2 (hid x Co)
-        for c_ in calls:
-            c_()
-        torch.cuda.synchronize()
-        gg = torch.cuda.CUDAGraph()
-        greps = 4
-        with torch.cuda.graph(gg):
-            for _ in range(greps):
-                for c_ in calls:
-                    c_()
-        gg.replay()
-        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
-        g0.record()
-        gg.replay()
-        g1.record()
-        torch.cuda.synchronize()
-        g_ms = g0.elapsed_time(g1) / greps
-        tpeak = None
-        try:
-            tpeak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"])
-        except Exception:
-            pass
-        ach = flops / (g_ms * 1e-3) / 1e12
-        gemm_roof = {"kernel": "gemm_tc_kernel", "bound": "tensor", "achieved": ach, "peak": tpeak, "unit": "TFLOP/s",
-                     "frac": ach / tpeak if tpeak else None, "traffic": None, "launches": len(calls),
-                     "flops_per_iteration": flops, "us_per_iteration": g_ms * 1000.0,
-                     "note": "the 30 pointwise-convolution GEMMs of one update iteration (SURVEY 8d: 114.4 GMAC minus the "
-                             "depthwise and mask-head terms), fused epilogues included, timed alone by graph replay; peak = "
-                             "measured dense bf16 burst figure"}
-        del calls
-
-    tmax = torch.tensor([ms, e2e_s * 1000.0], device=dev, dtype=torch.float64)
+    tmax = torch.tensor([ms, e2e_ms], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
     ms_max, e2e_ms_max = float(tmax[0]), float(tmax[1])
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
-    total = world * n_steps
+    total = job.n_total
+    per_rank = max(len(job.my_frames), 1)
     line = {
-        "metric": "MOF seq5 436x1024 flow frames/s", "value": total / (ms_max / 1000.0), "unit": "frames/s",
-        "n_gpus": world, "steps": n_steps, "warmup": warm, "ms_per_step": ms_max / n_steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "metric": cfg["metric"], "value": total / (ms_max / 1000.0), "unit": "frames/s", "n_gpus": world,
+        "steps": steps if cfg["scaling"] == "weak" else total, "warmup": n_warm, "ms_per_step": ms_max / per_rank,
+        "higher_is_better": True, "scaling": cfg["scaling"], "vs_baseline": None,
         "dtype": "f32" if args.precision == "fp32" else "f16", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "iterations": args.iters, "precision": args.precision,
-                   "l2": "inputs larger than L2 (%s of correlation volumes per window)" % ("1.58 GB" if args.precision == "fp32" else "811 MB"),
-                   "sharding": f"{world} rank(s), windows sharded, flows gathered to rank 0 (NCCL) inside the timed region"},
+        "config": {"workload": cfg["workload"], "config": args.config, "iterations": iters, "precision": args.precision,
+                   "clip_frames": total, "frames_per_rank": per_rank,
+                   "l2": "inputs larger than L2 (correlation volumes of one window: %s)" % ("1.58 GB" if args.precision == "fp32" else "811 MB at C1"),
+                   "feature_cache": "per-frame encoder outputs cached across the sliding windows of the clip; every frame is distinct "
+                                    "and every window new, so a steady-state window runs 1 fnet + 1 cnet pass (halo frames at shard starts "
+                                    "are re-encoded)" if cfg["arch"] != "memflow" else "n/a",
+                   "encoder_passes": stats,
+                   "sharding": f"{world} rank(s): ONE clip of {total} frames, " + (
+                       "tile chunks dealt by sharding.shard_tile_chunks, tiles summed into rank 0 (NCCL reduce)" if cfg["tile"] and world > 1
+                       else "replicas (a clip's memory is sequential)" if cfg["arch"] == "memflow"
+                       else "contiguous frame ranges (sharding.shard_range), flows gathered to rank 0 (NCCL)") + " inside the timed region"},
         "clocks": clocks,
-        "e2e": {"value": total / (e2e_ms_max / 1000.0), "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "e2e": {"value": total / (e2e_ms_max / 1000.0), "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "timing": "wall clock around the public-API calls (host numpy frames in, numpy out), barrier + synchronize on both sides"},
         "gpu_launches": int(launches),
-        "roofline": {"kernel": lk_kernel, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": NCU_TRAFFIC.get(lk_kernel), "peak_source": peak_kind,
-                     "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full capture of this command "
-                                       "(profiles/r1_lookup_tiled_ncu_summary.txt; cold L2)" if lk_kernel in NCU_TRAFFIC else None,
-                     "algorithmic_bytes_per_launch": alg_bytes, "us_per_launch": lk_ms * 1000.0},
     }
-    if gemm_roof is not None:
-        line["roofline_gemm"] = gemm_roof
-    if not args.no_cpu_baseline and world == 1:
-        t_enc, t_setup, t_iter, cores = cpu_port_times(2)
-        tw = t_enc + t_setup + ITERS * t_iter
-        line["cpu_baseline"] = {"value": 1.0 / tw, "unit": "frames/s", "cores": cores, "kind": "port",
-                                "sample": "oracle MOF window 436x1024 T=5 at full size: encoders + corr pyramids + attention + 2 "
-                                          "measured update iterations, extrapolated linearly to 32"}
-    print(json.dumps(line))
+    if rank == 0 and not args.no_extras and args.config == "C1" and hasattr(job, "proc"):
+        line.update(c1_extras(torch, ops, job, cfg, args, iters, dev, world))
+    if rank == 0:
+        print(json.dumps(line))
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
+
+
+def c1_extras(torch, ops, job, cfg, args, iters, dev, world):
+    """Rank 0, config C1: the numbers that explain the headline (kernel rooflines, the self-contained-window path of round 1,
+    the exact fp32 tier, the reference's op sequence on this GPU and on the host cores, the lookup comparators)."""
+    import cases
+    extra = {}
+    eng = job.proc.core.model
+    T, H, W = cfg["T"], cfg["H"], cfg["W"]
+    hp, wp, Fc = (H + 7) // 8, (W + 7) // 8, T - 2
+    # ---- round-1 measurement: every window self-contained (window tensor resident, T + (T-2) encoder passes, no cache)
+    frames = cases.sliding_clip(200000, 200008, H, W, seed=1234)
+    wins = [job.proc.prepare_frame_sequence(frames, i) for i in range(8)]
+    out = torch.empty((8, 2, H, W), dtype=torch.float32, device=dev)
+    for i in range(3):
+        job.proc.core.compute_flow_from_tensor(wins[i], out=out[i])
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(8):
+        job.proc.core.compute_flow_from_tensor(wins[i], out=out[i])
+    e1.record()
+    torch.cuda.synchronize()
+    extra["value_uncached"] = {"value": 8000.0 / e0.elapsed_time(e1), "unit": "frames/s", "ms_per_step": e0.elapsed_time(e1) / 8,
+                               "note": "compute_flow_from_tensor on resident window tensors: 5 fnet + 3 cnet passes per window (round-1 'value')"}
+    # ---- kernel rooflines
+    if eng.dt == torch.float16:
+        extra["roofline"] = roofline_gemm(torch, ops, eng, Fc, hp * wp, dev)
+    with torch.no_grad():
+        fmaps, _, _ = eng.encode(torch.nn.functional.pad(wins[0], [0, 0, 2, 2, 0, 0], mode="replicate"))
+    lk = roofline_lookup(torch, ops, eng, fmaps.float().contiguous(), Fc, hp, wp, dev)
+    if "roofline" in extra:
+        extra["roofline_lookup"] = lk
+    else:
+        extra["roofline"] = lk
+    # ---- lookup comparators (BASELINE.md B-lookup-ref / B-altcorr), one direction, Fc frames, microseconds per call
+    try:
+        extra["lookup_comparators"] = lookup_comparators(torch, fmaps.float(), Fc, hp, wp, dev)
+    except Exception as e:
+        extra["lookup_comparators"] = {"error": f"{type(e).__name__}: {e}"[:200]}
+    del fmaps, wins
+    torch.cuda.empty_cache()
+    if world > 1:
+        return extra
+    # ---- the exact (fp32, <= 1e-2 px) tier, driver-timed
+    if args.precision != "fp32":
+        try:
+            j32 = FlowJob(cfg, dev, "fp32", iters, 1, 0, 3)
+            f32, n32 = j32.clip(offset=300000)
+            timed_job(torch, None, j32, 1, f32, n32, host_out=False)          # warm-up (graph capture)
+            f32, n32 = j32.clip(offset=310000)
+            ms32, _ = timed_job(torch, None, j32, 1, f32, n32, host_out=False)
+            f32, n32 = j32.clip(offset=320000)
+            e32, _ = timed_job(torch, None, j32, 1, f32, n32, host_out=True)
+            extra["tiers"] = {"fp32": {"value": 3000.0 / ms32, "e2e": 3000.0 / e32, "unit": "frames/s", "steps": 3,
+                                       "note": "exact tier (FFMA kernels, <= 1e-2 px vs the reference on every fixture)"}}
+            del j32
+            torch.cuda.empty_cache()
+        except Exception as e:
+            extra["tiers"] = {"fp32": {"error": f"{type(e).__name__}: {e}"[:200]}}
+    # ---- the reference's op sequence on this GPU and on the host cores
+    extra["torch_gpu_baseline"] = torch_gpu_baseline(cfg, dev)
+    if not args.no_cpu_baseline:
+        r = cpu_oracle_timing(cfg, float(os.environ.get("VFML_CPU_BUDGET_S", "40")), 1)
+        extra["cpu_baseline"] = {"value": r["value"], "unit": "frames/s", "cores": r["cores"], "kind": "port", "sample": r["sample"],
+                                 "extrapolated": r["extrapolated"], "window_s": r["window_s"]}
+    return extra
+
+
+def lookup_comparators(torch, fmaps, Fc, hp, wp, dev):
+    """The reference's own lookup paths on this GPU at C1 shapes, one direction (Fc frames), microseconds per call:
+    CorrBlock.__call__ = 4x grid_sample on the fp32 pyramid (corr.py:76-97, utils.py:62-76; through the pinned oracle
+    restatement), and alt_cuda_corr.forward x 4 levels (correlation_kernel.cu:18-119, the reference's sources compiled
+    for sm_100 into oracle/_ref by oracle/build_ref.py) when that build exists."""
+    from oracle import mof as omof
+    res = {}
+    f1, f2 = fmaps[1:1 + Fc].contiguous(), fmaps[2:2 + Fc].contiguous()
+    g = torch.Generator(device="cpu").manual_seed(3)
+    coords = (omof.pixel_grid(Fc, hp, wp) + 8.0 * torch.randn((Fc, 2, hp, wp), generator=g)).to(dev)
+
+    def time_us(fn, n=10):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return 1000.0 * e0.elapsed_time(e1) / n
+    with torch.no_grad():
+        pyr = omof.corr_pyramid(f1, f2)
+        res["corrblock_grid_sample_us"] = time_us(lambda: omof.corr_lookup(pyr, coords))
+        del pyr
+        from oracle import build_ref
+        mod = build_ref.load_alt_cuda_corr()
+        if mod is None:
+            res["alt_cuda_corr_sm100_us"] = None
+            res["alt_cuda_corr_note"] = "oracle/_ref/alt_cuda_corr not built (python oracle/build_ref.py in the build container)"
+        else:
+            n1 = f1.permute(0, 2, 3, 1).contiguous()
+            pyr2 = [f2]
+            for _ in range(3):
+                pyr2.append(torch.nn.functional.avg_pool2d(pyr2[-1], 2, stride=2))
+            pyr2 = [p.permute(0, 2, 3, 1).contiguous() for p in pyr2]
+            c = coords.permute(0, 2, 3, 1)
+
+            def alt():
+                return [mod.forward(n1, pyr2[i], (c / 2 ** i).reshape(Fc, 1, hp, wp, 2).contiguous(), 4)[0] for i in range(4)]
+            res["alt_cuda_corr_sm100_us"] = time_us(alt)
+    return res
 
 
 if __name__ == "__main__":

@@ -98,7 +98,7 @@ def bof_refine(fmaps, net, inp, sd, iters=ITERS):
     pyr21 = omof.corr_pyramid(fmaps[1:2], fmaps[0:1])
     pyr23 = omof.corr_pyramid(fmaps[1:2], fmaps[2:3])
     attn = omof.gma_attention(inp, sd)
-    c0 = omof.pixel_grid(1, h, w)
+    c0 = omof.pixel_grid(1, h, w, fmaps.device)
     c21, c23 = c0.clone(), c0.clone()
     out = None
     for it in range(iters):

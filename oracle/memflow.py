@@ -226,7 +226,7 @@ class InferenceCore:
         query, key, net, inp = encode_context(images[:, 0], sd)
         fmaps = encode_features(images, sd)
         B, _, h, w = query.shape
-        coords0 = omof.pixel_grid(B, h, w)
+        coords0 = omof.pixel_grid(B, h, w, query.device)
         coords1 = coords0.clone() if flow_init is None else coords0 + flow_init
         pyr = omof.corr_pyramid(fmaps[:, 0], fmaps[:, 1])
         qf, kf = query.flatten(2), key.flatten(2)

@@ -47,9 +47,9 @@ def unpad(x, ht, wd, mode="sintel"):
     return x[..., t:H - b, l:W - r]
 
 
-def pixel_grid(n, h, w):
+def pixel_grid(n, h, w, device=None):
     """[n,2,h,w], channel 0 = x, channel 1 = y. utils.py:97-100"""
-    ys, xs = torch.meshgrid(torch.arange(h), torch.arange(w), indexing="ij")
+    ys, xs = torch.meshgrid(torch.arange(h, device=device), torch.arange(w, device=device), indexing="ij")
     return torch.stack([xs, ys], 0).float()[None].repeat(n, 1, 1, 1)
 
 
@@ -91,7 +91,7 @@ def corr_lookup(pyr, coords, radius=CORR_RADIUS):
     n = 2 * r + 1
     c = coords.permute(0, 2, 3, 1)
     B, h, w, _ = c.shape
-    d = torch.linspace(-r, r, n)
+    d = torch.linspace(-r, r, n, device=coords.device)
     # stack(meshgrid(dy, dx)) added to (x, y): first grid (varies along dim 0) goes to x
     off = torch.stack(torch.meshgrid(d, d, indexing="ij"), -1).view(1, n, n, 2)
     out = []
@@ -192,7 +192,7 @@ def motion_encoder(mhs, ffl, bfl, coords0, fcorr, bcorr, bs, sd, p="update_block
         mhs = sd[p + ".init_hidden_state"].repeat(bs, N, 1, H, W)
     else:
         mhs = mhs.reshape(bs, N, -1, H, W)
-    z = torch.zeros(bs, 1, 48, H, W)
+    z = torch.zeros(bs, 1, 48, H, W, device=ffl.device)
     nxt = torch.cat([mhs[:, 1:], z], 1).reshape(BN, -1, H, W)       # state of frame t+1
     prv = torch.cat([z, mhs[:, :N - 1]], 1).reshape(BN, -1, H, W)   # state of frame t-1
     fw = sample_px(nxt.float(), (ffl + coords0).permute(0, 2, 3, 1))
@@ -234,25 +234,26 @@ def convex_upsample8(flow, mask):
 # ----------------------------------------------------------------------------
 # network                              MOF/network.py:138-215
 # ----------------------------------------------------------------------------
-def mof_encode(images, sd, encoder=None):
+def mof_encode(images, sd, encoder=None, amp=None):
     """images [1,T,3,H,W] (raw caller values) -> fmaps [T,256,h,w], net/inp [T-2,128,h,w].
     network.py:144-170.  ``encoder(x, prefix)`` overrides the Twins restatement."""
     B, T, _, H, W = images.shape
     x = 2 * (images / 255.0) - 1.0
     enc = encoder or (lambda im, pre: twins_svt_forward(im, sd, pre + ".svt"))
-    fmaps = enc(x.reshape(B * T, 3, H, W), "fnet").float()
-    cnet = enc(x[:, 1:T - 1].reshape(B * (T - 2), 3, H, W), "cnet")
-    net, inp = torch.split(cnet, [128, 128], dim=1)
-    return fmaps, torch.tanh(net), torch.relu(inp)
+    with _amp(amp, images.device.type):          # network.py:149,160: both encoders run under autocast on CUDA
+        fmaps = enc(x.reshape(B * T, 3, H, W), "fnet").float()
+        cnet = enc(x[:, 1:T - 1].reshape(B * (T - 2), 3, H, W), "cnet")
+        net, inp = torch.split(cnet, [128, 128], dim=1)
+        return fmaps, torch.tanh(net), torch.relu(inp)
 
 
-def _amp(dtype):
+def _amp(dtype, device_type="cpu"):
     """Emulation of the reference's CUDA mixed-precision path (network.py:13,149,160,191: encoders, attention and
     the update block under fp16 autocast; volume build and lookup in fp32, network.py:151 / corr.py:97) with
     torch's CPU autocast.  Used only to measure the reference's OWN reduced-precision deviation (the noise floor
     the fp16 tier is compared with, scripts/fp16_floor.py); dtype=None is the fp32 path."""
     import contextlib
-    return torch.autocast("cpu", dtype=dtype) if dtype is not None else contextlib.nullcontext()
+    return torch.autocast(device_type, dtype=dtype) if dtype is not None else contextlib.nullcontext()
 
 
 def mof_refine(fmaps, net, inp, sd, iters=ITERS, all_iters=False, trace=None, amp=None):
@@ -264,9 +265,10 @@ def mof_refine(fmaps, net, inp, sd, iters=ITERS, all_iters=False, trace=None, am
     h, w = fmaps.shape[-2:]
     fpyr = corr_pyramid(fmaps[1:T - 1], fmaps[2:T])
     bpyr = corr_pyramid(fmaps[1:T - 1], fmaps[0:T - 2])
-    with _amp(amp):
+    dt_ = fmaps.device.type
+    with _amp(amp, dt_):
         attn = gma_attention(inp, sd)
-    c0 = pixel_grid(Fc, h, w)
+    c0 = pixel_grid(Fc, h, w, fmaps.device)
     fc1, bc1 = c0.clone(), c0.clone()
     mhs = None
     outs = []
@@ -274,7 +276,7 @@ def mof_refine(fmaps, net, inp, sd, iters=ITERS, all_iters=False, trace=None, am
         fcorr = corr_lookup(fpyr, fc1)
         bcorr = corr_lookup(bpyr, bc1)
         last = it == iters - 1
-        with _amp(amp):
+        with _amp(amp, dt_):
             net, mhs, mask, delta = update_block(net, mhs, inp, fcorr, bcorr, fc1 - c0, bc1 - c0, c0, attn, 1, sd,
                                                  with_mask=(last or all_iters))
         fc1 = fc1 + delta[:, 0:2]

@@ -105,3 +105,42 @@ def mof_case(seed=29, n_frames=6, H=124, W=188, as_float=True):
     (double normalisation, near-constant features)."""
     fr = synthetic_clip(n_frames, H, W, seed=seed, max_shift=10.0)
     return [f.astype(np.float32) for f in fr] if as_float else fr
+
+
+_TEX = {}
+
+
+def _texture(height, width, seed):
+    """The multi-octave smooth noise texture of synthetic_clip (same construction), cached per size."""
+    key = (height, width, seed)
+    if key not in _TEX:
+        r = rng(seed)
+        H, W = height + 128, width + 128
+        tex = np.zeros((H, W, 3), np.float32)
+        for octave in range(5):
+            s = 2 ** (octave + 2)
+            g = r.standard_normal((H // s + 2, W // s + 2, 3)).astype(np.float32)
+            tex += np.kron(g, np.ones((s, s, 1), np.float32))[:H, :W] / (octave + 1)
+        k = np.array([1, 4, 6, 4, 1], np.float32) / 16
+        for ax in (0, 1):
+            tex = sum(np.roll(tex, i - 2, axis=ax) * k[i] for i in range(5))
+        _TEX.clear()
+        _TEX[key] = (tex - tex.min()) / (tex.max() - tex.min())
+    return _TEX[key]
+
+
+def sliding_clip(start, stop, height, width, seed=1234, max_shift=24.0):
+    """Frames [start, stop) of an endless synthetic clip (bench.py): like synthetic_clip, but frame t depends only on
+    (seed, t) -- a bounded Lissajous translation of the texture plus 2 % salt noise drawn from a per-frame generator --
+    so every rank of a sharded job can generate just its own range, and no two frames are ever equal."""
+    tex = _texture(height, width, seed)
+    frames = []
+    for t in range(start, stop):
+        dx = int(np.clip(64 + round(max_shift * 2.0 * np.sin(0.31 * t) + 12 * np.sin(0.047 * t)), 0, 128))
+        dy = int(np.clip(64 + round(max_shift * 1.0 * np.cos(0.23 * t) + 8 * np.sin(0.061 * t)), 0, 128))
+        f = tex[dy:dy + height, dx:dx + width]
+        r = np.random.default_rng([seed, t])
+        salt = r.random((height, width, 1), dtype=np.float32) < 0.02
+        f = np.where(salt, r.random((height, width, 3), dtype=np.float32), f)
+        frames.append((f * 255).astype(np.uint8))
+    return frames

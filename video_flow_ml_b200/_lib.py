@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvfml.so")
+LIB_PATH = os.environ.get("VFML_LIB_PATH") or os.path.join(_HERE, "libvfml.so")     # override: A/B builds of the same ABI
 
 F32, F16 = 0, 1
 NCHW, ROWS = 0, 1

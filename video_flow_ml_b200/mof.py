@@ -134,6 +134,7 @@ class MOFEngine:
         self._ws = {}                    # (Fc, h, w) -> workspace; a small LRU (tile mode alternates between 2-3 shapes)
         self.max_workspaces = int(os.environ.get("VFML_MAX_WORKSPACES", "3"))
         self.use_graph = use_graph
+        self.vol_dtype = None            # untiled tiers only: storage type of the volume (default: the tier's dtype)
         self.lookup_math_f32 = False     # fp16x2 interpolation: 2.43e-2 px vs 2.37e-2 px (fp32) end to end, 8 % faster
         self.graph_launches = 0          # kernels executed through CUDA-graph replays (not seen by vfml_launch_count)
         self.use_side_stream = os.environ.get("VFML_NO_SIDE_STREAM") is None
@@ -328,8 +329,9 @@ class MOFEngine:
             ws = ws or {}
             return (self.ops.corr_volume_pyramid_tiled(c, fmaps[2:T].contiguous(), ws.get("vol_ws"), out=ws.get("fpyr")),
                     self.ops.corr_volume_pyramid_tiled(c, fmaps[0:T - 2].contiguous(), ws.get("vol_ws"), out=ws.get("bpyr")))
-        fw = self.ops.corr_volume_pyramid(c, fmaps[2:T].contiguous(), CORR_LEVELS, self.dt)
-        bw = self.ops.corr_volume_pyramid(c, fmaps[0:T - 2].contiguous(), CORR_LEVELS, self.dt)
+        vdt = self.vol_dtype or self.dt
+        fw = self.ops.corr_volume_pyramid(c, fmaps[2:T].contiguous(), CORR_LEVELS, vdt)
+        bw = self.ops.corr_volume_pyramid(c, fmaps[0:T - 2].contiguous(), CORR_LEVELS, vdt)
         return fw, bw
 
     def attention(self, ws, Fc, P):

@@ -32,6 +32,7 @@ class VideoFlowProcessor:
         # computation per call, for callers that rewrite frame arrays in place between calls.
         self.feature_cache = True
         self._dev_frames = collections.OrderedDict()      # frame key -> device tensor [H, W, 3]
+        self.device_frame_capacity = None                 # frames kept on the device (default: two windows' worth)
 
     def load_model(self):
         model_path = self.core.load_model()
@@ -133,7 +134,7 @@ class VideoFlowProcessor:
         else:
             t = torch.from_numpy(np.ascontiguousarray(f, dtype=np.float32)).to(self.device)
         self._dev_frames[key] = t
-        while len(self._dev_frames) > 2 * max(self.sequence_length, 5):
+        while len(self._dev_frames) > (self.device_frame_capacity or 2 * max(self.sequence_length, 5)):
             self._dev_frames.popitem(last=False)
         return t
 
@@ -214,15 +215,7 @@ class VideoFlowProcessor:
             if tile_pbar is not None:
                 tile_pbar.set_description("Running VideoFlow")
                 tile_pbar.reset()
-            x, y, w, h = ti['x'], ti['y'], ti['width'], ti['height']
-            if cw is not None:          # per-(frame, tile) encoder cache; the frame itself is uploaded once for all its tiles
-                seq, keys = cw
-                rect = (x, y, w, h)
-                lazy = [(lambda f=f, k=k: self._chw(self._device_frame(f, k), rect)) for f, k in zip(seq, keys)]
-                self.core.compute_flow_from_frames(lazy, [k + rect for k in keys], out=full[:, y:y + h, x:x + w])
-            else:
-                tile = window[..., y:y + h, x:x + w].contiguous()
-                self.core.compute_flow_from_tensor(tile, out=full[:, y:y + h, x:x + w])
+            self._compute_tile(cw, window, ti, full)
             if tile_pbar is not None:
                 tile_pbar.set_description("Completed")
                 tile_pbar.update(4)
@@ -231,6 +224,24 @@ class VideoFlowProcessor:
         if return_device:
             return full.permute(1, 2, 0)
         return full.permute(1, 2, 0).cpu().numpy()
+
+    def _compute_tile(self, cw, window, ti, full):
+        """One tile of one output frame, written by the upsampling kernel into its place in `full` [2, H, W]."""
+        x, y, w, h = ti['x'], ti['y'], ti['width'], ti['height']
+        if cw is not None:          # per-(frame, tile) encoder cache; the frame itself is uploaded once for all its tiles
+            seq, keys = cw
+            rect = (x, y, w, h)
+            lazy = [(lambda f=f, k=k: self._chw(self._device_frame(f, k), rect)) for f, k in zip(seq, keys)]
+            self.core.compute_flow_from_frames(lazy, [k + rect for k in keys], out=full[:, y:y + h, x:x + w])
+        else:
+            tile = window[..., y:y + h, x:x + w].contiguous()
+            self.core.compute_flow_from_tensor(tile, out=full[:, y:y + h, x:x + w])
+
+    def compute_tile_into(self, frames, frame_idx, tile_info, full):
+        """Sharded tile mode (sharding.shard_tile_chunks): compute ONE tile of frame `frame_idx` into `full` [2, H, W]."""
+        cw = self._cached_window(frames, frame_idx)
+        window = self.prepare_frame_sequence(frames, frame_idx) if cw is None else None
+        self._compute_tile(cw, window, tile_info, full)
 
     # ------------------------------------------------------------------ misc API
     def is_model_loaded(self):

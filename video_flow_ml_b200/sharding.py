@@ -28,6 +28,30 @@ def shard_tiles(frame_ids, tiles_info, world_size, rank):
     return items[rank::world_size]
 
 
+def shard_tile_chunks(n_frames, tiles_info, world_size, rank, chunk=4):
+    """Tile mode over one clip: work units are (tile, contiguous frame range) chunks, so that consecutive frames of the
+    SAME tile stay on one rank and its per-(frame, tile) encoder cache keeps working (a (frame, tile) item costs T + (T-2)
+    encoder passes cold and 1 + 1 behind its predecessor).  Chunks are dealt largest-first to the least-loaded rank
+    (ragged edge tiles weigh less).  -> this rank's list of (tile_index, frame_start, frame_stop), and every rank's load."""
+    if world_size < 1 or not (0 <= rank < world_size):
+        raise ValueError(f"bad rank {rank} / world size {world_size}")
+    units = []
+    for ti, t in enumerate(tiles_info):
+        for a in range(0, n_frames, chunk):
+            b = min(n_frames, a + chunk)
+            units.append((t['width'] * t['height'] * (b - a), ti, a, b))
+    units.sort(key=lambda u: (-u[0], u[1], u[2]))
+    load = [0] * world_size
+    mine = []
+    for cost, ti, a, b in units:
+        r = min(range(world_size), key=lambda i: (load[i], i))
+        load[r] += cost
+        if r == rank:
+            mine.append((ti, a, b))
+    mine.sort()
+    return mine, load
+
+
 def gather_flows(local, n_total, world_size, rank, dst=0, group=None):
     """local: [n_local, 2, H, W] flows of this rank's contiguous shard (shard_range order).
     Returns the [n_total, 2, H, W] clip on `dst`, None elsewhere.  Shards may differ in length by one, so they
