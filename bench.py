@@ -68,24 +68,53 @@ def host_cores():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """SM clock and throttle reasons during the timed region (the B200_PROFILING.md clocks line).  Read through NVML in
+    process (the library nvidia-smi itself uses): forking nvidia-smi every 200 ms from a process that maps tens of GB of
+    device memory stalls the launching thread for tens of milliseconds per fork.  Falls back to nvidia-smi without NVML."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.rows, self.stop_evt = index, [], threading.Event()
+        self.nv = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else index
+            self.nv = (pynvml, pynvml.nvmlDeviceGetHandleByIndex(phys))
+        except Exception:
+            self.nv = None
+
+    def _sample(self):
+        if self.nv is not None:
+            nv, h = self.nv
+            sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            try:
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+            except Exception:
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+            bit = lambda name, alt: getattr(nv, name, getattr(nv, alt, 0))
+            flags = [bool(r & bit("nvmlClocksEventReasonHwSlowdown", "nvmlClocksThrottleReasonHwSlowdown")),
+                     bool(r & bit("nvmlClocksEventReasonHwThermalSlowdown", "nvmlClocksThrottleReasonHwThermalSlowdown")),
+                     bool(r & bit("nvmlClocksEventReasonSwThermalSlowdown", "nvmlClocksThrottleReasonSwThermalSlowdown")),
+                     bool(r & bit("nvmlClocksEventReasonSwPowerCap", "nvmlClocksThrottleReasonSwPowerCap"))]
+            return [str(sm), str(mx)] + ["Active" if f else "Not Active" for f in flags]
+        out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                             capture_output=True, text=True, timeout=5).stdout.strip()
+        return [c.strip() for c in out.split(",")] if out else None
 
     def run(self):
         while not self.stop_evt.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
+                row = self._sample()
+                if row:
+                    self.rows.append(row)
             except Exception:
                 pass
-            self.stop_evt.wait(0.2)
+            self.stop_evt.wait(0.1 if self.nv is not None else 0.5)
 
     def summary(self):
         self.stop_evt.set()
@@ -96,7 +125,8 @@ class ClockSampler(threading.Thread):
             if any(len(r) > i and r[i].lower().startswith("active") for r in self.rows):
                 reasons.append(name)
         mx = max((int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()), default=None)
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons, "samples": len(sm)}
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons, "samples": len(sm),
+                "source": "NVML (in process)" if self.nv is not None else "nvidia-smi"}
 
 
 # ------------------------------------------------------------------------------------------ CPU oracle (reference arm)
