@@ -316,6 +316,11 @@ int vfml_motion_glue(const float* fcoords, const float* bcoords, void* x400, int
                      const float* convf1_w, const float* convf1_b, int n_frames, int h, int w,
                      int dtype, vfml_stream_t s);
 
+/* Twins PEG (PosConv, VideoFlow/core/Networks/twins_ft.py:341-355): y = x + dwconv3x3(x) + b on token-major rows
+ * [n_img*h*w, C] (fp32 or fp16; C multiple of 4 / 8), weight tap-major [9, C] and bias [C] in the same dtype. */
+int vfml_peg3x3(const void* x, void* y, int n_img, int h, int w, int C, int64_t ld_x, int64_t ld_y, const void* weight,
+                const void* bias, int dtype, vfml_stream_t s);
+
 /* coords[n,2,h,w] (+)= delta rows: fcoords += delta[:, 0:2]; bcoords += delta[:, 2:4] (network.py:196-197) */
 int vfml_coords_add(float* fcoords, float* bcoords, const float* delta, int64_t ld_delta, int n_frames,
                     int hw, vfml_stream_t s);

@@ -21,6 +21,9 @@ class StubEngine:
             return m.expand(-1, 128, 2, 3).clone(), (m + 1).expand(-1, 128, 2, 3).clone()
         return (2 * m).expand(-1, 256, 2, 3).clone()
 
+    def encode_new_frames(self, xf, xc):
+        return (None if xf is None else self.encode_frames(xf)), (None if xc is None else self.encode_frames(xc, context=True))
+
     def refine(self, fmaps, net, inp, select=None, crop=None, out=None):
         self.last = (fmaps[:, 0, 0, 0].clone(), net[:, 0, 0, 0].clone(), inp[:, 0, 0, 0].clone(), select, crop)
         return torch.zeros(2, crop[2], crop[3])

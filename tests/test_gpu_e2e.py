@@ -375,12 +375,16 @@ def test_feature_cache_equals_uncached_and_saves_encoder_passes():
         want = p.compute_optical_flow(frames, i)
         assert np.abs(want - g_).max() <= 1e-3, (i, np.abs(want - g_).max())
     assert p.core.cache_stats == st
-    # a frame rewritten in place is noticed
+    # a frame rewritten in place is noticed: its features are recomputed (uint8 frames take the reference's double
+    # normalisation, SURVEY Q1, so the flow itself barely depends on the content: the encoder pass count is the evidence)
     p.set_feature_cache(True)
-    a = p.compute_optical_flow(frames, 3)
+    p.compute_optical_flow(frames, 3)
+    before = dict(p.core.cache_stats)
+    p.compute_optical_flow(frames, 3)
+    assert p.core.cache_stats["fnet_runs"] == before["fnet_runs"]            # unchanged frames: all hits
     frames[3][:] = frames[3][::-1].copy()
-    b = p.compute_optical_flow(frames, 3)
-    assert np.abs(a - b).max() > 1e-3
+    p.compute_optical_flow(frames, 3)
+    assert p.core.cache_stats["fnet_runs"] == before["fnet_runs"] + 1 and p.core.cache_stats["cnet_runs"] == before["cnet_runs"] + 1
 
 
 def test_device_resident_post_pass_matches_reference_golden(golden):

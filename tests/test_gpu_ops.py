@@ -528,3 +528,39 @@ def test_layer_norm_rows_matches_torch(ops, dt, tol, shape):
     with pytest.raises(RuntimeError):
         ops.layer_norm_rows(torch.zeros((4, 10), device="cuda", dtype=dt), torch.ones(10, device="cuda", dtype=dt),
                             torch.zeros(10, device="cuda", dtype=dt), 1e-6)
+
+
+def test_peg3x3_matches_conv2d():
+    """Twins PEG kernel (x + dwconv3x3(x) + b, token-major) against torch's conv2d in fp64 on the CPU."""
+    from video_flow_ml_b200 import ops
+    g = torch.Generator().manual_seed(3)
+    for (B, H, W, C) in ((1, 20, 20, 256), (2, 13, 7, 128), (3, 55, 64, 8)):
+        x = torch.randn((B, H * W, C), generator=g)
+        wt = torch.randn((C, 1, 3, 3), generator=g) * 0.3
+        b = torch.randn((C,), generator=g)
+        m = x.double().transpose(1, 2).reshape(B, C, H, W)
+        want = (m + torch.nn.functional.conv2d(m, wt.double(), b.double(), padding=1, groups=C)).flatten(2).transpose(1, 2)
+        for dt, tol in ((torch.float32, 1e-5), (torch.float16, 2e-2)):
+            got = ops.peg3x3(x.cuda().to(dt).contiguous(), B, H, W, wt.reshape(C, 9).t().contiguous().cuda().to(dt), b.cuda().to(dt))
+            ref = want if dt == torch.float32 else (x.half().double().transpose(1, 2).reshape(B, C, H, W) + torch.nn.functional.conv2d(
+                x.half().double().transpose(1, 2).reshape(B, C, H, W), wt.half().double(), b.half().double(), padding=1, groups=C)).flatten(2).transpose(1, 2)
+            assert (got.double().cpu() - ref).abs().max() <= tol, (B, H, W, C, dt)
+
+
+def test_twins_is_batch_independent():
+    """The encoders are per-image functions (the per-frame feature cache relies on it): one frame alone gives the same
+    features as inside a batch, in both tiers, also for small tiles.  (Regression: a library depthwise kernel returned
+    garbage for batch 1, 20x20, 256 channels, fp16.)"""
+    from oracle import mof as omof
+    from video_flow_ml_b200.twins import TwinsStage01
+    sd = omof.mof_synthetic_weights(0, gain=1.0)
+    g = torch.Generator().manual_seed(5)
+    for (H, W) in ((160, 160), (128, 128), (288, 448)):
+        x = (torch.rand((5, 3, H, W), generator=g) * 2 - 1).cuda()
+        for dt, tol in ((torch.float32, 1e-4), (torch.float16, 5e-2)):
+            for prefix in ("fnet.svt", "cnet.svt"):
+                enc = TwinsStage01(sd, prefix, "cuda", dt)
+                full = enc(x)
+                assert torch.isfinite(full).all()
+                for b in (1, 2):
+                    assert (enc(x[:b]) - full[:b]).abs().max() <= tol, (H, W, dt, prefix, b)

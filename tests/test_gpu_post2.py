@@ -37,9 +37,10 @@ def test_rgb8_hsv_torchvision_wrappers_bit_exact(golden):
 
 
 def test_encoders_full_size_vs_oracle():
-    """1080p adversarial field (large values, NaN / inf, exact clamp boundaries, ties): bit-exact for rgb8 / decode;
-    HSV and torchvision go through atan2, which numpy / Sleef do not round correctly everywhere: <= 1 LSB on <= 1e-4 of
-    the bytes (0 expected; the bound documents what libm differences could do)."""
+    """1080p adversarial field (large values, NaN / inf, exact clamp boundaries, ties): bit-exact for rgb8 / decode.
+    HSV and torchvision go through atan2; the kernels use the correctly rounded value, numpy (SIMD) / torch (Sleef) are
+    within 1 ulp of it, so a pixel whose hue or colour-wheel position sits within that ulp of an integer boundary can land
+    on the other side: at most 1e-5 of the pixels may differ (measured: 1 pixel of 2,073,600 for HSV, 0 for torchvision)."""
     from video_flow_ml_b200 import ops
     r = np.random.default_rng(5)
     f = (30 * r.standard_normal((1080, 1920, 2))).astype(np.float32)
@@ -57,9 +58,9 @@ def test_encoders_full_size_vs_oracle():
         for name, got, want in (("hsv", ops.encode_hsv(d).cpu().numpy(), opost.encode_hsv(f)),
                                 ("torchvision", ops.encode_torchvision(dev(np.nan_to_num(f, nan=0.0, posinf=9.0, neginf=-9.0))).cpu().numpy(),
                                  opost.encode_torchvision(np.nan_to_num(f, nan=0.0, posinf=9.0, neginf=-9.0)))):
-            diff = np.abs(got.astype(np.int16) - want.astype(np.int16))
-            diff = np.minimum(diff, 256 - diff)                   # the torchvision wrap is modulo 256
-            assert diff.max() <= 1 and (diff > 0).mean() <= 1e-4, (name, diff.max(), (diff > 0).sum())
+            bad = (got != want).any(-1)
+            print(f"{name}: {int(bad.sum())} of {bad.size} pixels differ")
+            assert bad.mean() <= 1e-5, (name, int(bad.sum()))
     nowrap = ops.encode_torchvision(dev(np.nan_to_num(f, nan=0.0, posinf=9.0, neginf=-9.0)), ref_wrap=False).cpu().numpy()
     assert np.array_equal((nowrap.astype(np.int32) * 255 % 256).astype(np.uint8),
                           ops.encode_torchvision(dev(np.nan_to_num(f, nan=0.0, posinf=9.0, neginf=-9.0))).cpu().numpy())

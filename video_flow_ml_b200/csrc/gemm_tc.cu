@@ -29,6 +29,9 @@ constexpr int TC_BM = 128, TC_BK = 64;
 #ifndef VFML_TC_EPI_WARPS
 #define VFML_TC_EPI_WARPS 12
 #endif
+#ifndef VFML_TC_EPI_V1
+#define VFML_TC_EPI_V1 0          // 1 = the lane-per-row epilogue of round 1 (kept for A/B runs)
+#endif
 constexpr int TC_EPI_WARPS = VFML_TC_EPI_WARPS;      // multiple of 4: warp w may only read TMEM lanes 32 (w % 4) ..
 constexpr int TC_THREADS = 64 + TC_EPI_WARPS * 32;
 constexpr int TC_MAX_STAGES = 8;
@@ -134,6 +137,56 @@ __device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[16]) {
                  : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
                    "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
                  :: "memory");
+}
+
+
+// tcgen05.ld shape 16x256b, 8 repetitions: 16 TMEM lanes (rows) x 64 fp32 columns.  Thread t of the warp receives, for
+// every 8-column group g, r[4g + {0,1}] = row t / 4, columns 8g + 2 (t % 4) + {0,1} and r[4g + {2,3}] = row t / 4 + 8, same
+// columns (the mma C-fragment arrangement): the four lanes of a quad hold one row segment between them.
+__device__ __forceinline__ void tmem_ld_16x256b_x8_issue(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.16x256b.x8.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+          "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+          "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait32(uint32_t (&r)[32]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]),
+                   "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]), "+r"(r[16]), "+r"(r[17]), "+r"(r[18]),
+                   "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]),
+                   "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+                 :: "memory");
+}
+// 4 x 4 transpose of 32-bit words across the lanes of a quad: lane q passes row q of a matrix and receives column q.
+__device__ __forceinline__ void quad_transpose4(uint32_t& a0, uint32_t& a1, uint32_t& a2, uint32_t& a3, int q) {
+    const bool o1 = q & 1, o2 = q & 2;
+    uint32_t x0 = o1 ? a0 : a1, x1 = o1 ? a2 : a3;
+    x0 = __shfl_xor_sync(0xffffffffu, x0, 1);
+    x1 = __shfl_xor_sync(0xffffffffu, x1, 1);
+    if (o1) { a0 = x0; a2 = x1; } else { a1 = x0; a3 = x1; }
+    x0 = o2 ? a0 : a2; x1 = o2 ? a1 : a3;
+    x0 = __shfl_xor_sync(0xffffffffu, x0, 2);
+    x1 = __shfl_xor_sync(0xffffffffu, x1, 2);
+    if (o2) { a0 = x0; a1 = x1; } else { a2 = x0; a3 = x1; }
+}
+// Row-contiguous words R[k] (lane q of the quad holds columns 16 q + 2 k, + 1 of a 64-column row segment, k = 0..7)  <->
+// fragment words F[g] (columns 8 g + 2 q, + 1): R[4 b + j] = F_lane j [2 s + b] for lane s, i.e. two quad transposes.
+__device__ __forceinline__ void quad_frag_to_rows(uint32_t (&w)[8], int q) {
+    quad_transpose4(w[0], w[2], w[4], w[6], q);      // b = 0: F[0], F[2], F[4], F[6] -> R[0..3]
+    quad_transpose4(w[1], w[3], w[5], w[7], q);      // b = 1: F[1], F[3], F[5], F[7] -> R[4..7]
+    const uint32_t r1 = w[2], r2 = w[4], r3 = w[6], r4 = w[1], r5 = w[3], r6 = w[5];
+    w[1] = r1; w[2] = r2; w[3] = r3; w[4] = r4; w[5] = r5; w[6] = r6;
+}
+__device__ __forceinline__ void quad_rows_to_frag(uint32_t (&w)[8], int q) {
+    uint32_t a0 = w[0], a1 = w[1], a2 = w[2], a3 = w[3], b0 = w[4], b1 = w[5], b2 = w[6], b3 = w[7];
+    quad_transpose4(a0, a1, a2, a3, q);              // -> F[0], F[2], F[4], F[6]
+    quad_transpose4(b0, b1, b2, b3, q);              // -> F[1], F[3], F[5], F[7]
+    w[0] = a0; w[2] = a1; w[4] = a2; w[6] = a3; w[1] = b0; w[3] = b1; w[5] = b2; w[7] = b3;
 }
 
 // shared-memory matrix descriptor, K-major, 128-byte swizzle: 8-row groups of 128 B rows, 1024 B apart
@@ -322,6 +375,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         }
         if (tr && lane == 0) { p.trace[blockIdx.x * 8 + 2] = t_we; p.trace[blockIdx.x * 8 + 3] = t_wf; p.trace[blockIdx.x * 8 + 4] = clock64() - t0; }
     } else {
+#if VFML_TC_EPI_V1
         long long e_wait = 0, e_t0 = clock64();
         const int q = warp & 3;                   // TMEM lane quarter this warp may access
         const int hsel = (warp - 2) >> 2;         // which CONTIGUOUS share of the tile's columns (contiguous: a thread's
@@ -506,6 +560,169 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             if (lane == 0) mbar_arrive(&acc_empty[buf]);
         }
         if (p.trace && warp == 2 && lane == 0) { p.trace[blockIdx.x * 8 + 5] = e_wait; p.trace[blockIdx.x * 8 + 6] = clock64() - e_t0; }
+#else
+        // ---- epilogue, row-segment version.  Each of this warp's accesses to global memory covers 8 rows x 128 contiguous
+        // bytes: the accumulator is read in the 16x256b shape (a quad of lanes holds one row segment), the fused math runs
+        // in that fragment layout, and two 4x4 quad transposes per row turn the fp16 result (and the residual on its way in)
+        // into 32 contiguous bytes per lane.  The lane-per-row version (VFML_TC_EPI_V1) issued one 32-byte sector per lane
+        // and row -- 32 L2 requests per instruction -- and the in-kernel trace showed the MMA warp waiting for accumulators
+        // 60 % of the time on the residual layers (profiles/r2_gemm_trace.txt).
+        long long e_wait = 0, e_t0 = clock64();
+        const int q4 = warp & 3;                  // TMEM lane quarter this warp may access
+        const int cg = (warp - 2) >> 2;           // units (64-column chunk, 16-row half) are dealt round-robin over the
+        constexpr int NCS = TC_EPI_WARPS / 4;     // NCS warps of a quarter
+        constexpr bool SP = SPEC >= 0;
+        const uint32_t epi = SP ? (uint32_t)SPEC : p.epi;
+        const bool has_bias = epi & VFML_EPI_BIAS, has_res = epi & VFML_EPI_RES, has_dw = epi & VFML_EPI_DW1;
+        const bool do_gelu = epi & VFML_EPI_GELU, do_relu = epi & VFML_EPI_RELU;
+        const bool out_f32 = SP ? false : (bool)p.out_f32, vec_smem = SP ? true : (bool)p.vec_in_smem;
+        const float2 alpha2 = splat(p.alpha);
+        const int qd = lane & 3, rl = lane >> 2;
+        uint32_t tl = 0;
+        for (int tile = t_first; tile < t_end; tile += t_step, ++tl) {
+            int bz, m0, n0;
+            tile_coords(tile, bz, m0, n0);
+            const uint32_t buf = tl & 1u, aph = (tl >> 1) & 1u;
+            const int cols_here = min(BN, p.N - n0);
+            const int n_units = ((cols_here + 63) >> 6) * 2;
+            const __half* rbase = p.res ? p.res + bz * p.strideR : nullptr;
+            __half* d16b = reinterpret_cast<__half*>(p.D) + bz * p.strideD;
+            float* d32b = reinterpret_cast<float*>(p.D) + bz * p.strideD;
+            // vector path: 16-byte aligned rows (warp-uniform: the quad transposes are collective)
+            const bool d_vec = !out_f32 && ((reinterpret_cast<uintptr_t>(d16b) & 15) == 0) && ((p.ldd & 7) == 0) && ((n0 & 7) == 0);
+            const bool r_vec = has_res && ((reinterpret_cast<uintptr_t>(rbase) & 15) == 0) && ((p.ldr & 7) == 0) && ((n0 & 7) == 0);
+            const long long ew0 = clock64();
+            mbar_wait(&acc_full[buf], aph);
+            e_wait += clock64() - ew0;
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            // residual rows of a unit, row-contiguous words (lane qd: columns c + 16 qd .. + 15 of rows rA, rA + 8)
+            auto load_res = [&](int u, uint32_t (&ra)[8], uint32_t (&rb)[8]) {
+                const int c = (u >> 1) << 6;
+                const int mA = m0 + q4 * 32 + (u & 1) * 16 + rl;
+                const int n = n0 + c + 16 * qd;
+#pragma unroll
+                for (int s2 = 0; s2 < 2; ++s2) {
+                    uint32_t (&r)[8] = s2 ? rb : ra;
+                    const int m = mA + 8 * s2;
+                    const __half* rp = rbase + (int64_t)m * p.ldr + n;
+                    if (m < p.M && n + 16 <= p.N && r_vec) {
+                        const uint4 v0 = *reinterpret_cast<const uint4*>(rp), v1 = *reinterpret_cast<const uint4*>(rp + 8);
+                        r[0] = v0.x; r[1] = v0.y; r[2] = v0.z; r[3] = v0.w; r[4] = v1.x; r[5] = v1.y; r[6] = v1.z; r[7] = v1.w;
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) {
+                            const __half lo = (m < p.M && n + 2 * k < p.N) ? rp[2 * k] : __float2half_rn(0.0f);
+                            const __half hi = (m < p.M && n + 2 * k + 1 < p.N) ? rp[2 * k + 1] : __float2half_rn(0.0f);
+                            r[k] = (uint32_t)__half_as_ushort(lo) | ((uint32_t)__half_as_ushort(hi) << 16);
+                        }
+                    }
+                }
+            };
+            uint32_t ra[8], rb[8];
+            int u = cg;
+            if (has_res && u < n_units) load_res(u, ra, rb);
+            for (; u < n_units; u += NCS) {
+                const int c = (u >> 1) << 6, hf = u & 1;
+                uint32_t acc[32];
+                tmem_ld_16x256b_x8_issue(tmem_base + buf * 256u + (uint32_t)c + ((uint32_t)(q4 * 32 + hf * 16) << 16), acc);
+                uint32_t fa[8], fb[8];                 // residual in fragment layout
+                if (has_res) {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) { fa[k] = ra[k]; fb[k] = rb[k]; }
+                    quad_rows_to_frag(fa, qd);
+                    quad_rows_to_frag(fb, qd);
+                    if (u + NCS < n_units) load_res(u + NCS, ra, rb);      // next unit's residual flies during this unit's math
+                }
+                tmem_ld_wait32(acc);
+                const int mA = m0 + q4 * 32 + hf * 16 + rl;
+                uint32_t oa[8], ob[8];                 // fp16 results, fragment layout
+#pragma unroll
+                for (int g = 0; g < 8; ++g) {
+                    const int n = n0 + c + 8 * g + 2 * qd;           // this lane's two columns of group g
+                    const int nv = min(n, vec_cols - 2);             // columns past the tile's last one are computed, never stored
+                    float2 xa = make_float2(__uint_as_float(acc[4 * g]), __uint_as_float(acc[4 * g + 1]));
+                    float2 xb = make_float2(__uint_as_float(acc[4 * g + 2]), __uint_as_float(acc[4 * g + 3]));
+                    if (!SP) { xa = mul2(xa, alpha2); xb = mul2(xb, alpha2); }
+                    if (has_bias) {
+                        float2 b2;
+                        if (vec_smem) b2 = *reinterpret_cast<const float2*>(s_vec + nv);         // indexed by absolute column
+                        else b2 = make_float2(__ldg(p.bias + min(n, p.N - 1)), __ldg(p.bias + min(n + 1, p.N - 1)));
+                        xa = add2(xa, b2); xb = add2(xb, b2);
+                    }
+                    if (has_res) {
+                        xa = add2(xa, __half22float2(*reinterpret_cast<const __half2*>(&fa[g])));
+                        xb = add2(xb, __half22float2(*reinterpret_cast<const __half2*>(&fb[g])));
+                    }
+                    if (do_gelu) { xa = gelu_fast2(xa); xb = gelu_fast2(xb); }
+                    if (do_relu) {
+                        xa = make_float2(fmaxf(xa.x, 0.0f), fmaxf(xa.y, 0.0f));
+                        xb = make_float2(fmaxf(xb.x, 0.0f), fmaxf(xb.y, 0.0f));
+                    }
+                    if (has_dw) {   // k = 1 depthwise stage: gelu(v + (w * v + b))
+                        float2 w2, b2;
+                        if (vec_smem) {
+                            w2 = *reinterpret_cast<const float2*>(s_vec + vec_cols + nv);
+                            b2 = *reinterpret_cast<const float2*>(s_vec + 2 * vec_cols + nv);
+                        } else {
+                            const int n1 = min(n, p.N - 1), n2 = min(n + 1, p.N - 1);
+                            w2 = make_float2(__ldg(p.dw_w + n1), __ldg(p.dw_w + n2));
+                            b2 = make_float2(__ldg(p.dw_b + n1), __ldg(p.dw_b + n2));
+                        }
+                        xa = gelu_fast2(add2(xa, fma2(w2, xa, b2)));
+                        xb = gelu_fast2(add2(xb, fma2(w2, xb, b2)));
+                    }
+                    if (out_f32) {          // fp32 outputs (logits, partial sums, delta, mask) leave in fragment layout: 8 B per lane
+                        float* da = d32b + (int64_t)mA * p.ldd + n;
+                        float* db = da + 8 * p.ldd;
+                        const bool al = ((reinterpret_cast<uintptr_t>(d32b) & 7) == 0) && ((p.ldd & 1) == 0) && ((n & 1) == 0);
+                        if (mA < p.M) {
+                            if (n + 1 < p.N && al) *reinterpret_cast<float2*>(da) = xa;
+                            else { if (n < p.N) da[0] = xa.x; if (n + 1 < p.N) da[1] = xa.y; }
+                        }
+                        if (mA + 8 < p.M) {
+                            if (n + 1 < p.N && al) *reinterpret_cast<float2*>(db) = xb;
+                            else { if (n < p.N) db[0] = xb.x; if (n + 1 < p.N) db[1] = xb.y; }
+                        }
+                    } else {
+                        const __half2 ha = __float22half2_rn(xa), hb = __float22half2_rn(xb);
+                        oa[g] = *reinterpret_cast<const uint32_t*>(&ha);
+                        ob[g] = *reinterpret_cast<const uint32_t*>(&hb);
+                    }
+                }
+                if (!out_f32) {
+                    quad_frag_to_rows(oa, qd);
+                    quad_frag_to_rows(ob, qd);
+                    const int n = n0 + c + 16 * qd;
+#pragma unroll
+                    for (int s2 = 0; s2 < 2; ++s2) {
+                        const uint32_t (&o)[8] = s2 ? ob : oa;
+                        const int m = mA + 8 * s2;
+                        if (m >= p.M) continue;
+                        __half* dp = d16b + (int64_t)m * p.ldd + n;
+                        if (n + 16 <= p.N && d_vec) {
+                            const uint4 v0 = make_uint4(o[0], o[1], o[2], o[3]), v1 = make_uint4(o[4], o[5], o[6], o[7]);
+                            if ((reinterpret_cast<uintptr_t>(dp) & 31) == 0) st_global_256(dp, v0, v1);
+                            else {
+                                *reinterpret_cast<uint4*>(dp) = v0;
+                                *reinterpret_cast<uint4*>(dp + 8) = v1;
+                            }
+                        } else {
+#pragma unroll
+                            for (int k = 0; k < 8; ++k) {
+                                if (n + 2 * k < p.N) dp[2 * k] = __ushort_as_half((unsigned short)(o[k] & 0xffffu));
+                                if (n + 2 * k + 1 < p.N) dp[2 * k + 1] = __ushort_as_half((unsigned short)(o[k] >> 16));
+                            }
+                        }
+                    }
+                }
+            }
+            // this warp is done reading the accumulator: hand it back to the MMA warp
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[buf]);
+        }
+        if (p.trace && warp == 2 && lane == 0) { p.trace[blockIdx.x * 8 + 5] = e_wait; p.trace[blockIdx.x * 8 + 6] = clock64() - e_t0; }
+#endif
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();

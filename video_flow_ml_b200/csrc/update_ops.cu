@@ -267,6 +267,53 @@ __global__ void __launch_bounds__(256) layer_norm_rows_kernel(const T* __restric
     }
 }
 
+// Positional-encoding generator of the Twins encoder (PosConv, twins_ft.py:341-355; encoders.py:27-29,35-37):
+// y = x + dwconv3x3(x) + b on token-major rows [n * h * w, C], zero padding.  One thread = one pixel x one 16-byte channel
+// vector, fp32 accumulation; weights tap-major [9, C] in the activations' dtype.  (Also replaces a cuDNN depthwise kernel
+// that returned wrong values for batch 1 / 20x20 / 256 channels in fp16 on this stack.)
+template <typename T>
+__global__ void __launch_bounds__(256) peg3x3_kernel(const T* __restrict__ x, T* __restrict__ y, int n_img, int h, int w, int C,
+                                                     int64_t ldx, int64_t ldy, const T* __restrict__ wgt, const T* __restrict__ bias) {
+    constexpr int E = 16 / (int)sizeof(T);
+    const int cv = C / E;
+    const int64_t total = (int64_t)n_img * h * w * cv;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(i % cv) * E;
+        const int64_t pix = i / cv;
+        const int px = (int)(pix % w), py = (int)((pix / w) % h);
+        float acc[E];
+        {
+            const uint4 b4 = *reinterpret_cast<const uint4*>(bias + c);
+            const T* b = reinterpret_cast<const T*>(&b4);
+#pragma unroll
+            for (int j = 0; j < E; ++j) acc[j] = to_f32<T>(b[j]);
+        }
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) {
+            const int yy = py + ky - 1;
+            if (yy < 0 || yy >= h) continue;
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+                const int xx = px + kx - 1;
+                if (xx < 0 || xx >= w) continue;
+                const uint4 v4 = *reinterpret_cast<const uint4*>(x + (pix + (int64_t)(ky - 1) * w + (kx - 1)) * ldx + c);
+                const uint4 w4 = *reinterpret_cast<const uint4*>(wgt + (ky * 3 + kx) * C + c);
+                const T* v = reinterpret_cast<const T*>(&v4);
+                const T* wv = reinterpret_cast<const T*>(&w4);
+#pragma unroll
+                for (int j = 0; j < E; ++j) acc[j] = fmaf(to_f32<T>(v[j]), to_f32<T>(wv[j]), acc[j]);
+            }
+        }
+        const uint4 c4 = *reinterpret_cast<const uint4*>(x + pix * ldx + c);
+        const T* cv_ = reinterpret_cast<const T*>(&c4);
+        uint4 o4;
+        T* o = reinterpret_cast<T*>(&o4);
+#pragma unroll
+        for (int j = 0; j < E; ++j) o[j] = from_f32<T>(to_f32<T>(cv_[j]) + acc[j]);
+        *reinterpret_cast<uint4*>(y + pix * ldy + c) = o4;
+    }
+}
+
 __global__ void coords_add_kernel(float* __restrict__ fc, float* __restrict__ bc, const float* __restrict__ delta,
                                   int64_t ld, int F, int hw) {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // lets a PDL-launched successor start its prologue
@@ -444,6 +491,24 @@ extern "C" int vfml_layer_norm_rows(const void* x, void* y, int64_t rows, int C,
     }
 #undef VFML_LN_CASE
     VFML_LAUNCH_CHECK("layer_norm_rows");
+    return VFML_OK;
+}
+
+extern "C" int vfml_peg3x3(const void* x, void* y, int n_img, int h, int w, int C, int64_t ld_x, int64_t ld_y, const void* weight,
+                           const void* bias, int dtype, vfml_stream_t s) {
+    VFML_REQUIRE(valid_dtype(dtype), "peg3x3: bad dtype");
+    const int E = dtype == VFML_F16 ? 8 : 4;
+    VFML_REQUIRE(n_img >= 0 && h > 0 && w > 0 && C > 0 && (C % E) == 0 && ld_x >= C && ld_y >= C && (ld_x % E) == 0 && (ld_y % E) == 0,
+                 "peg3x3: C and the pitches must be multiples of %d", E);
+    if (n_img == 0) return VFML_OK;
+    VFML_REQUIRE(x && y && weight && bias && x != y, "peg3x3: null pointer or in-place call");
+    auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+    VFML_REQUIRE(al(x) && al(y) && al(weight) && al(bias), "peg3x3: pointers must be 16-byte aligned");
+    const int64_t total = (int64_t)n_img * h * w * (C / E);
+    const int blocks = (int)std::min<int64_t>(cdiv(total, 256), device_sms() * 16);
+    DISPATCH_T(dtype, (peg3x3_kernel<float><<<blocks, 256, 0, to_stream(s)>>>((const float*)x, (float*)y, n_img, h, w, C, ld_x, ld_y, (const float*)weight, (const float*)bias)),
+               (peg3x3_kernel<__half><<<blocks, 256, 0, to_stream(s)>>>((const __half*)x, (__half*)y, n_img, h, w, C, ld_x, ld_y, (const __half*)weight, (const __half*)bias)));
+    VFML_LAUNCH_CHECK("peg3x3");
     return VFML_OK;
 }
 

@@ -314,12 +314,55 @@ class MOFEngine:
         """Per-frame halves of `encode` for the feature cache (fnet and cnet are per-image functions, network.py:150,161):
         frames [n, 3, H, W] (raw caller values, already padded) -> fmaps [n, 256, h, w] (context=False) or the context
         encoder's (tanh(net), relu(inp)) [n, 128, h, w] each (context=True)."""
+        fm, ctx = self.encode_new_frames(None if context else frames, frames if context else None)
+        return ctx if context else fm
+
+    def _encode_new_body(self, xf, xc):
+        fm = ctx = None
+        if xc is not None:
+            if xf is not None:
+                self._fork_side()                           # the context encoder runs beside the feature encoder
+            net, inp = torch.split(self.cnet(2 * (xc.float() / 255.0) - 1.0), [128, 128], dim=1)
+            ctx = (torch.tanh(net).float().contiguous(), torch.relu(inp).float().contiguous())
+            if xf is not None:
+                self._back_to_main()
+        if xf is not None:
+            fm = self.fnet(2 * (xf.float() / 255.0) - 1.0).float()
+            if xc is not None:
+                self._join_side()
+                for t in ctx:
+                    if t.is_cuda:
+                        t.record_stream(torch.cuda.current_stream(t.device))
+        return fm, ctx
+
+    @torch.no_grad()
+    def encode_new_frames(self, xf, xc):
+        """Encoders on the frames a window adds to the cache: xf [nf, 3, H, W] -> fmaps [nf, 256, h, w], xc [nc, 3, H, W] ->
+        (tanh(net), relu(inp)) [nc, 128, h, w] each; either may be None.  The two encoders run on two streams, and the
+        steady-state shapes (one new frame each: ~60 small library launches per encoder) are replayed from a CUDA graph."""
         with self._guard():
-            x = 2 * (frames.float() / 255.0) - 1.0
-            if not context:
-                return self.fnet(x).float()
-            net, inp = torch.split(self.cnet(x), [128, 128], dim=1)
-            return torch.tanh(net).float().contiguous(), torch.relu(inp).float().contiguous()
+            if not (self.use_graph and self.dev.type == "cuda" and max(0 if xf is None else xf.shape[0], 0 if xc is None else xc.shape[0]) <= 1):
+                return self._encode_new_body(xf, xc)
+            key = (None if xf is None else tuple(xf.shape), None if xc is None else tuple(xc.shape))
+            graphs = self.__dict__.setdefault("_enc_graphs", {})
+            g = graphs.pop(key, None)
+            if g is None:
+                while len(graphs) >= 4:
+                    graphs.pop(next(iter(graphs)))
+                static = [None if t is None else t.float().clone() for t in (xf, xc)]
+                self._encode_new_body(*static)              # eager warm-up (library handles, autotuning) before the capture
+                torch.cuda.synchronize(self.dev)
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    out = self._encode_new_body(*static)
+                g = {"graph": graph, "static": static, "out": out}
+            graphs[key] = g
+            for s_, t in zip(g["static"], (xf, xc)):
+                if t is not None:
+                    s_.copy_(t)
+            g["graph"].replay()
+            fm, ctx = g["out"]       # static outputs: the cache keeps copies
+            return (None if fm is None else fm.clone()), (None if ctx is None else (ctx[0].clone(), ctx[1].clone()))
 
     def build_pyramids(self, fmaps, ws=None):
         """Forward (frames 1..T-2 vs 2..T-1) and backward (vs 0..T-3) pyramids, network.py:157-158."""

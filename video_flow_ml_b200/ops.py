@@ -566,6 +566,19 @@ def layer_norm_rows(x, weight, bias, eps):
     return y
 
 
+def peg3x3(x, n_img, h, w, weight_tapmajor, bias):
+    """Twins PEG: x + dwconv3x3(x) + b on a contiguous token-major tensor [n_img, h*w, C]; weight [9, C], same dtype."""
+    _cuda(x, weight_tapmajor, bias)
+    Cc = x.shape[-1]
+    if not x.is_contiguous() or x.numel() != n_img * h * w * Cc or weight_tapmajor.shape != (9, Cc) or bias.numel() != Cc \
+            or not (x.dtype == weight_tapmajor.dtype == bias.dtype):
+        raise ValueError("peg3x3: shape / dtype mismatch")
+    y = torch.empty_like(x)
+    _lib.check(_lib.load().vfml_peg3x3(_p(x), _p(y), n_img, h, w, Cc, Cc, Cc, _p(weight_tapmajor.contiguous()), _p(bias.contiguous()),
+                                       _dt(x), _stream()), "peg3x3")
+    return y
+
+
 def softmax_rows(src, dst):
     _cuda(src, dst)
     _rows(src, "src"); _rows(dst, "dst")

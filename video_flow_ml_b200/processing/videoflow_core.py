@@ -155,17 +155,17 @@ class VideoFlowCore:
         uniq_c = sorted({first[keys[i] if keys[i] is not None else ("#", i)] for i in need_c})
         with torch.no_grad():
             new = {}
-            if uniq_f:
-                fm = self.model.encode_frames(torch.cat([tensor(j)[0] for j in uniq_f]))
-                for n, j in enumerate(uniq_f):
-                    new[j] = {"fmap": fm[n], "ctx": None, "hw": tensor(j)[1:]}
-                self.cache_stats["fnet_runs"] += len(uniq_f)
-            if uniq_c:
-                net, inp = self.model.encode_frames(torch.cat([tensor(j)[0] for j in uniq_c]), context=True)
-                for n, j in enumerate(uniq_c):
-                    e = new.get(j) or ent[j]
-                    e["ctx"] = (net[n], inp[n])
-                self.cache_stats["cnet_runs"] += len(uniq_c)
+            same = uniq_f == uniq_c and len(uniq_f) > 0
+            xf = torch.cat([tensor(j)[0] for j in uniq_f]) if uniq_f else None
+            xc = xf if same else (torch.cat([tensor(j)[0] for j in uniq_c]) if uniq_c else None)
+            fm, ctx = self.model.encode_new_frames(xf, xc) if (uniq_f or uniq_c) else (None, None)      # the two encoders side by side
+            for n, j in enumerate(uniq_f):
+                new[j] = {"fmap": fm[n], "ctx": None, "hw": tensor(j)[1:]}
+            for n, j in enumerate(uniq_c):
+                e = new.get(j) or ent[j]
+                e["ctx"] = (ctx[0][n], ctx[1][n])
+            self.cache_stats["fnet_runs"] += len(uniq_f)
+            self.cache_stats["cnet_runs"] += len(uniq_c)
             self.cache_stats["fnet_hits"] += Tn - len(need_f)
             self.cache_stats["cnet_hits"] += len(centre) - len(need_c)
             for i in range(Tn):

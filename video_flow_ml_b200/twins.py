@@ -7,8 +7,9 @@ the reference tree, so the math follows the class definitions vendored in
 VideoFlow/core/Networks/twins_ft.py: PatchEmbed :361-386, LocallyGroupedAttn :214-261,
 GlobalSubSampleAttn :264-312, Block :315-338, PosConv :341-355, svt_large :509-515.
 Weights keep timm's key names (``<prefix>.patch_embeds.0.proj.weight`` ...), so upstream
-checkpoints load unchanged.  This part is NOT a libvfml kernel: it is per-image work that the
-engine caches per frame; native kernels for it are the first "next" item of SURVEY 8(f).
+checkpoints load unchanged.  LayerNorm and the PEG depthwise convolution are libvfml kernels; the linear layers,
+the strided patch / sub-sampling convolutions and the attention products are library calls (cuBLAS / cuDNN / SDPA).  The
+outputs are per-image, so VideoFlowCore.compute_flow_from_frames caches them per frame across sliding windows.
 """
 import torch
 import torch.nn.functional as F
@@ -31,6 +32,9 @@ class TwinsStage01:
         self.p = {k[n:]: v.to(device=device, dtype=dtype) for k, v in state_dict.items()
                   if k.startswith(prefix + ".") and v.is_floating_point()}
         self.dtype = dtype
+        # PEG weights tap-major [9, C] for the libvfml kernel
+        self.peg = {s_: self.p[f"pos_block.{s_}.proj.0.weight"].reshape(-1, 9).t().contiguous() for s_ in range(2)
+                    if f"pos_block.{s_}.proj.0.weight" in self.p}
 
     def _ln(self, x, name, eps):
         w, b = self.p[name + ".weight"], self.p[name + ".bias"]
@@ -61,7 +65,9 @@ class TwinsStage01:
         B, N, C = x.shape
         hd = C // heads
         q = self._fc(x, name + ".q").view(B, N, heads, hd).transpose(1, 2)
-        y = F.conv2d(x.transpose(1, 2).reshape(B, C, H, W), self.p[name + ".sr.weight"], self.p[name + ".sr.bias"], stride=sr)
+        # .contiguous(): a [1, C, H, W] view of token-major data is stride-ambiguous (NCHW or channels-last); the library's
+        # kernel choice for such views has produced wrong results at batch 1 (see ops.peg3x3)
+        y = F.conv2d(x.transpose(1, 2).reshape(B, C, H, W).contiguous(), self.p[name + ".sr.weight"], self.p[name + ".sr.bias"], stride=sr)
         y = self._ln(y.flatten(2).transpose(1, 2), name + ".norm", 1e-5)
         kv = self._fc(y, name + ".kv").view(B, -1, 2, heads, hd).permute(2, 0, 3, 1, 4)
         o = F.scaled_dot_product_attention(q, kv[0], kv[1])
@@ -100,8 +106,11 @@ class TwinsStage01:
                 x = x + self._fc(F.gelu(self._fc(y, blk + ".mlp.fc1")), blk + ".mlp.fc2")
                 if j == 0:   # PEG after the first block of each stage (encoders.py:27-29, :35-37)
                     pb = f"pos_block.{s}.proj.0"
-                    m = x.transpose(1, 2).reshape(B, -1, H, W)
-                    m = m + F.conv2d(m, self.p[pb + ".weight"], self.p[pb + ".bias"], padding=1, groups=m.shape[1])
-                    x = m.flatten(2).transpose(1, 2)
-            x = x.transpose(1, 2).reshape(B, -1, H, W)
+                    if x.is_cuda:      # libvfml kernel on the token-major layout (no NCHW round trip)
+                        x = _ops().peg3x3(x.contiguous(), B, H, W, self.peg[s], self.p[pb + ".bias"])
+                    else:
+                        m = x.transpose(1, 2).reshape(B, -1, H, W)
+                        m = m + F.conv2d(m, self.p[pb + ".weight"], self.p[pb + ".bias"], padding=1, groups=m.shape[1])
+                        x = m.flatten(2).transpose(1, 2)
+            x = x.transpose(1, 2).reshape(B, -1, H, W).contiguous()
         return x.float().contiguous()
