@@ -58,11 +58,13 @@ __device__ __forceinline__ float tanh_approx(float x) {
     return y;
 }
 __device__ __forceinline__ float2 gelu_tanh2(float2 x) {
-    const float2 xc = make_float2(fminf(fmaxf(x.x, -7.0f), 7.0f), fminf(fmaxf(x.y, -7.0f), 7.0f));
-    const float2 x2 = mul2(xc, xc);
+    // the fit holds for x^2 <= 49; beyond it the polynomial is frozen at its value there (1.79), so g = 1.79 x, |g| > 12.5
+    // and tanh saturates to +-1 exactly as the true atanh(erf) does: one min per element instead of a two-sided clamp of x
+    float2 x2 = mul2(x, x);
+    x2 = make_float2(fminf(x2.x, 49.0f), fminf(x2.y, 49.0f));
     float2 q = fma2(splat(-3.41174769e-04f), x2, splat(3.69255454e-02f));
     q = fma2(q, x2, splat(7.97627597e-01f));
-    const float2 t = mul2(xc, q);
+    const float2 t = mul2(x, q);
     const float2 th = make_float2(tanh_approx(t.x), tanh_approx(t.y));
     const float2 hx = mul2(x, splat(0.5f));
     return fma2(hx, th, hx);

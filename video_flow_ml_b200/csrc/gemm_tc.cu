@@ -30,7 +30,10 @@ constexpr int TC_BM = 128, TC_BK = 64;
 #define VFML_TC_EPI_WARPS 12
 #endif
 #ifndef VFML_TC_EPI_V1
-#define VFML_TC_EPI_V1 0          // 1 = the lane-per-row epilogue of round 1 (kept for A/B runs)
+#define VFML_TC_EPI_V1 1          // 1 = lane-per-row epilogue (default); 0 = the row-segment variant (16x256b TMEM loads + quad
+                                  // transposes, 8 rows x 128 B per access): measured equal within noise (profiles/r2_gemm_epilogue_ab.txt),
+                                  // because the epilogue is bound by its math issue slots and by ~19 B/clk/SM of store bandwidth, not by
+                                  // the number of L2 requests
 #endif
 constexpr int TC_EPI_WARPS = VFML_TC_EPI_WARPS;      // multiple of 4: warp w may only read TMEM lanes 32 (w % 4) ..
 constexpr int TC_THREADS = 64 + TC_EPI_WARPS * 32;
@@ -52,7 +55,7 @@ struct TcParams {
     int vec_in_smem;
     int b_res;           // weight-stationary mode: this CTA's B tile (all K blocks) stays in shared memory
     int b_is_const;      // B (and bias / dw vectors) are weights: may be fetched before the preceding kernel has finished
-    long long* trace;    // debug (VFML_GEMM_TRACE=1): per-CTA cycle counters, 8 per CTA
+    long long* trace;    // debug (VFML_GEMM_TRACE=1): per-CTA cycle counters, 16 per CTA
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -317,7 +320,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 if (++s == stages) { s = 0; ph ^= 1u; }
             }
         }
-        if (tr && lane == 0) { p.trace[blockIdx.x * 8 + 0] = t_wait; p.trace[blockIdx.x * 8 + 1] = clock64() - t0; }
+        if (tr && lane == 0) { p.trace[blockIdx.x * 16 + 0] = t_wait; p.trace[blockIdx.x * 16 + 1] = clock64() - t0; }
     } else if (warp == 1) {
         // instruction descriptor: D fp32, A/B fp16, both K-major, N = BN, M = 128
         const uint32_t idesc = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
@@ -373,7 +376,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             buf ^= 1u;
             aph ^= buf ^ 1u;       // flips each time buf wraps back to 0
         }
-        if (tr && lane == 0) { p.trace[blockIdx.x * 8 + 2] = t_we; p.trace[blockIdx.x * 8 + 3] = t_wf; p.trace[blockIdx.x * 8 + 4] = clock64() - t0; }
+        if (tr && lane == 0) { p.trace[blockIdx.x * 16 + 2] = t_we; p.trace[blockIdx.x * 16 + 3] = t_wf; p.trace[blockIdx.x * 16 + 4] = clock64() - t0; }
     } else {
 #if VFML_TC_EPI_V1
         long long e_wait = 0, e_t0 = clock64();
@@ -396,10 +399,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             const __half* rrow = p.res ? p.res + bz * p.strideR + (int64_t)m * p.ldr : nullptr;
             __half* d16 = reinterpret_cast<__half*>(p.D) + bz * p.strideD + (int64_t)m * p.ldd;
             float* d32 = reinterpret_cast<float*>(p.D) + bz * p.strideD + (int64_t)m * p.ldd;
-            const long long ew0 = clock64();
-            mbar_wait(&acc_full[buf], aph);
-            e_wait += clock64() - ew0;
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             // software pipeline over this warp's 16-column chunks: the TMEM load and the residual load of
             // chunk i+1 are in flight while chunk i goes through the epilogue math and is stored
             const bool res_vec = has_res && row_ok && ((reinterpret_cast<uintptr_t>(rrow) & 15) == 0) && ((n0 & 7) == 0);
@@ -416,15 +415,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 #else
             const int c_end = min(c + share, BN);
 #endif
+            // the first chunk's residual does not depend on the MMA: it is fetched while this warp waits for the accumulator
+            if (c < c_end && n0 + c < p.N && res_vec && n0 + c + 16 <= p.N) {
+                if (res_256) ld_global_256(rrow + n0 + c, rc0, rc1);
+                else {
+                    rc0 = *reinterpret_cast<const uint4*>(rrow + n0 + c);
+                    rc1 = *reinterpret_cast<const uint4*>(rrow + n0 + c + 8);
+                }
+            }
+            const long long ew0 = clock64();
+            mbar_wait(&acc_full[buf], aph);
+            e_wait += clock64() - ew0;
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             if (c < c_end && n0 + c < p.N) {
                 tmem_ld16_issue(trow + (uint32_t)c, tc);
-                if (res_vec && n0 + c + 16 <= p.N) {
-                    if (res_256) ld_global_256(rrow + n0 + c, rc0, rc1);
-                    else {
-                        rc0 = *reinterpret_cast<const uint4*>(rrow + n0 + c);
-                        rc1 = *reinterpret_cast<const uint4*>(rrow + n0 + c + 8);
-                    }
-                }
                 tmem_ld_wait(tc);
             }
             for (; c < c_end; c += 16) {
@@ -559,7 +563,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_empty[buf]);
         }
-        if (p.trace && warp == 2 && lane == 0) { p.trace[blockIdx.x * 8 + 5] = e_wait; p.trace[blockIdx.x * 8 + 6] = clock64() - e_t0; }
+        if (p.trace && warp == 2 && lane == 0) { p.trace[blockIdx.x * 16 + 5] = e_wait; p.trace[blockIdx.x * 16 + 6] = clock64() - e_t0; }
 #else
         // ---- epilogue, row-segment version.  Each of this warp's accesses to global memory covers 8 rows x 128 contiguous
         // bytes: the accumulator is read in the 16x256b shape (a quad of lanes holds one row segment), the fused math runs
@@ -568,6 +572,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         // and row -- 32 L2 requests per instruction -- and the in-kernel trace showed the MMA warp waiting for accumulators
         // 60 % of the time on the residual layers (profiles/r2_gemm_trace.txt).
         long long e_wait = 0, e_t0 = clock64();
+        long long e_ld = 0, e_res = 0, e_math = 0, e_st = 0;       // VFML_GEMM_TRACE: where a unit's time goes (warp 2)
+        const bool etr = p.trace != nullptr;
         const int q4 = warp & 3;                  // TMEM lane quarter this warp may access
         const int cg = (warp - 2) >> 2;           // units (64-column chunk, 16-row half) are dealt round-robin over the
         constexpr int NCS = TC_EPI_WARPS / 4;     // NCS warps of a quarter
@@ -585,6 +591,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             const uint32_t buf = tl & 1u, aph = (tl >> 1) & 1u;
             const int cols_here = min(BN, p.N - n0);
             const int n_units = ((cols_here + 63) >> 6) * 2;
+            const int n_lim = n0 + cols_here;          // a 64-column chunk may reach past the tile's last column: never touch those
             const __half* rbase = p.res ? p.res + bz * p.strideR : nullptr;
             __half* d16b = reinterpret_cast<__half*>(p.D) + bz * p.strideD;
             float* d32b = reinterpret_cast<float*>(p.D) + bz * p.strideD;
@@ -605,14 +612,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     uint32_t (&r)[8] = s2 ? rb : ra;
                     const int m = mA + 8 * s2;
                     const __half* rp = rbase + (int64_t)m * p.ldr + n;
-                    if (m < p.M && n + 16 <= p.N && r_vec) {
+                    if (m < p.M && n + 16 <= n_lim && r_vec) {
                         const uint4 v0 = *reinterpret_cast<const uint4*>(rp), v1 = *reinterpret_cast<const uint4*>(rp + 8);
                         r[0] = v0.x; r[1] = v0.y; r[2] = v0.z; r[3] = v0.w; r[4] = v1.x; r[5] = v1.y; r[6] = v1.z; r[7] = v1.w;
                     } else {
 #pragma unroll
                         for (int k = 0; k < 8; ++k) {
-                            const __half lo = (m < p.M && n + 2 * k < p.N) ? rp[2 * k] : __float2half_rn(0.0f);
-                            const __half hi = (m < p.M && n + 2 * k + 1 < p.N) ? rp[2 * k + 1] : __float2half_rn(0.0f);
+                            const __half lo = (m < p.M && n + 2 * k < n_lim) ? rp[2 * k] : __float2half_rn(0.0f);
+                            const __half hi = (m < p.M && n + 2 * k + 1 < n_lim) ? rp[2 * k + 1] : __float2half_rn(0.0f);
                             r[k] = (uint32_t)__half_as_ushort(lo) | ((uint32_t)__half_as_ushort(hi) << 16);
                         }
                     }
@@ -624,6 +631,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             for (; u < n_units; u += NCS) {
                 const int c = (u >> 1) << 6, hf = u & 1;
                 uint32_t acc[32];
+                long long tk0 = etr ? clock64() : 0;
                 tmem_ld_16x256b_x8_issue(tmem_base + buf * 256u + (uint32_t)c + ((uint32_t)(q4 * 32 + hf * 16) << 16), acc);
                 uint32_t fa[8], fb[8];                 // residual in fragment layout
                 if (has_res) {
@@ -633,7 +641,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     quad_rows_to_frag(fb, qd);
                     if (u + NCS < n_units) load_res(u + NCS, ra, rb);      // next unit's residual flies during this unit's math
                 }
+                long long tk1 = etr ? clock64() : 0;
                 tmem_ld_wait32(acc);
+                long long tk2 = etr ? clock64() : 0;
+                e_res += tk1 - tk0; e_ld += tk2 - tk1;
                 const int mA = m0 + q4 * 32 + hf * 16 + rl;
                 uint32_t oa[8], ob[8];                 // fp16 results, fragment layout
 #pragma unroll
@@ -676,12 +687,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                         float* db = da + 8 * p.ldd;
                         const bool al = ((reinterpret_cast<uintptr_t>(d32b) & 7) == 0) && ((p.ldd & 1) == 0) && ((n & 1) == 0);
                         if (mA < p.M) {
-                            if (n + 1 < p.N && al) *reinterpret_cast<float2*>(da) = xa;
-                            else { if (n < p.N) da[0] = xa.x; if (n + 1 < p.N) da[1] = xa.y; }
+                            if (n + 1 < n_lim && al) *reinterpret_cast<float2*>(da) = xa;
+                            else { if (n < n_lim) da[0] = xa.x; if (n + 1 < n_lim) da[1] = xa.y; }
                         }
                         if (mA + 8 < p.M) {
-                            if (n + 1 < p.N && al) *reinterpret_cast<float2*>(db) = xb;
-                            else { if (n < p.N) db[0] = xb.x; if (n + 1 < p.N) db[1] = xb.y; }
+                            if (n + 1 < n_lim && al) *reinterpret_cast<float2*>(db) = xb;
+                            else { if (n < n_lim) db[0] = xb.x; if (n + 1 < n_lim) db[1] = xb.y; }
                         }
                     } else {
                         const __half2 ha = __float22half2_rn(xa), hb = __float22half2_rn(xb);
@@ -689,6 +700,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                         ob[g] = *reinterpret_cast<const uint32_t*>(&hb);
                     }
                 }
+                long long tk3 = etr ? clock64() : 0;
+                e_math += tk3 - tk2;
                 if (!out_f32) {
                     quad_frag_to_rows(oa, qd);
                     quad_frag_to_rows(ob, qd);
@@ -699,7 +712,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                         const int m = mA + 8 * s2;
                         if (m >= p.M) continue;
                         __half* dp = d16b + (int64_t)m * p.ldd + n;
-                        if (n + 16 <= p.N && d_vec) {
+                        if (n + 16 <= n_lim && d_vec) {
                             const uint4 v0 = make_uint4(o[0], o[1], o[2], o[3]), v1 = make_uint4(o[4], o[5], o[6], o[7]);
                             if ((reinterpret_cast<uintptr_t>(dp) & 31) == 0) st_global_256(dp, v0, v1);
                             else {
@@ -709,19 +722,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                         } else {
 #pragma unroll
                             for (int k = 0; k < 8; ++k) {
-                                if (n + 2 * k < p.N) dp[2 * k] = __ushort_as_half((unsigned short)(o[k] & 0xffffu));
-                                if (n + 2 * k + 1 < p.N) dp[2 * k + 1] = __ushort_as_half((unsigned short)(o[k] >> 16));
+                                if (n + 2 * k < n_lim) dp[2 * k] = __ushort_as_half((unsigned short)(o[k] & 0xffffu));
+                                if (n + 2 * k + 1 < n_lim) dp[2 * k + 1] = __ushort_as_half((unsigned short)(o[k] >> 16));
                             }
                         }
                     }
                 }
+                if (etr) e_st += clock64() - tk3;
             }
             // this warp is done reading the accumulator: hand it back to the MMA warp
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_empty[buf]);
         }
-        if (p.trace && warp == 2 && lane == 0) { p.trace[blockIdx.x * 8 + 5] = e_wait; p.trace[blockIdx.x * 8 + 6] = clock64() - e_t0; }
+        if (p.trace && warp == 2 && lane == 0) {
+            p.trace[blockIdx.x * 16 + 5] = e_wait; p.trace[blockIdx.x * 16 + 6] = clock64() - e_t0;
+            p.trace[blockIdx.x * 16 + 8] = e_ld; p.trace[blockIdx.x * 16 + 9] = e_res; p.trace[blockIdx.x * 16 + 10] = e_math; p.trace[blockIdx.x * 16 + 11] = e_st;
+        }
 #endif
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -881,8 +898,8 @@ int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st) {
     long long*& trace_buf = trace_bufs.get();
     if (trace) {
         VFML_REQUIRE(grid <= TRACE_MAX_CTAS, "gemm_tc: VFML_GEMM_TRACE supports at most %d CTAs", TRACE_MAX_CTAS);
-        if (!trace_buf) VFML_CUDA(cudaMalloc(&trace_buf, TRACE_MAX_CTAS * 8 * sizeof(long long)));
-        VFML_CUDA(cudaMemsetAsync(trace_buf, 0, (size_t)grid * 8 * sizeof(long long), st));
+        if (!trace_buf) VFML_CUDA(cudaMalloc(&trace_buf, TRACE_MAX_CTAS * 16 * sizeof(long long)));
+        VFML_CUDA(cudaMemsetAsync(trace_buf, 0, (size_t)grid * 16 * sizeof(long long), st));
         p.trace = trace_buf;
     }
     // programmatic dependent launch: this kernel's prologue (and its resident weight tile) overlaps the tail of the
@@ -913,14 +930,14 @@ int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st) {
     }
     VFML_LAUNCH_CHECK("gemm_tc");
     if (trace) {      // debug only: synchronises
-        static long long h[TRACE_MAX_CTAS * 8];
-        VFML_CUDA(cudaMemcpyAsync(h, trace_buf, (size_t)grid * 8 * sizeof(long long), cudaMemcpyDeviceToHost, st));
+        static long long h[TRACE_MAX_CTAS * 16];
+        VFML_CUDA(cudaMemcpyAsync(h, trace_buf, (size_t)grid * 16 * sizeof(long long), cudaMemcpyDeviceToHost, st));
         VFML_CUDA(cudaStreamSynchronize(st));
-        double a[8] = {0};
+        double a[16] = {0};
         for (int c = 0; c < grid; ++c)
-            for (int i = 0; i < 8; ++i) a[i] += (double)h[c * 8 + i] / grid;
-        fprintf(stderr, "[gemm_tc trace] M=%d N=%d K=%d BN=%d stages=%d tiles=%lld epi=%u res=%d | producer wait_empty %.0f of %.0f | mma wait_acc_empty %.0f wait_full %.0f of %.0f | epilogue(warp2) wait_acc_full %.0f of %.0f cycles (avg per CTA)\n",
-                d.M, d.N, d.K, BN, stages, (long long)num_tiles, d.epi, (int)b_res, a[0], a[1], a[2], a[3], a[4], a[5], a[6]);
+            for (int i = 0; i < 16; ++i) a[i] += (double)h[c * 16 + i] / grid;
+        fprintf(stderr, "[gemm_tc trace] M=%d N=%d K=%d BN=%d stages=%d tiles=%lld epi=%u res=%d | producer wait_empty %.0f of %.0f | mma wait_acc_empty %.0f wait_full %.0f of %.0f | epilogue(warp2) wait_acc_full %.0f of %.0f cycles (avg per CTA) | epi phases: tmem_ld %.0f res %.0f math %.0f store %.0f\n",
+                d.M, d.N, d.K, BN, stages, (long long)num_tiles, d.epi, (int)b_res, a[0], a[1], a[2], a[3], a[4], a[5], a[6], a[8], a[9], a[10], a[11]);
     }
     return VFML_OK;
 }
