@@ -399,6 +399,9 @@ class MemFlowJob:
         x = u8.permute(2, 0, 1).float()[None]
         return self.torch.nn.functional.pad(2 * (x / 255.0) - 1.0, [0, 0] + self.pad[2:], mode="replicate")
 
+    def _unpad(self, up):
+        return up if self.crop is None else up[..., self.crop[0]:self.crop[0] + self.H, self.crop[1]:self.crop[1] + self.W]
+
     def upload(self, frames, need):
         self.dev_frames = [self._norm(self.torch.from_numpy(f).to(self.dev)) for f in frames]
 
@@ -412,13 +415,13 @@ class MemFlowJob:
                 np.copyto(self.pin.numpy(), f)
                 cur = self._norm(self.pin.to(self.dev, non_blocking=True))
                 if prev is not None:
-                    _, up = self.ic.step(torch.stack([prev[0], cur[0]])[None], crop=self.crop)
-                    self.last_np = up[0].permute(1, 2, 0).cpu().numpy()
+                    _, up = self.ic.step(torch.stack([prev[0], cur[0]])[None])
+                    self.last_np = self._unpad(up)[0].permute(1, 2, 0).cpu().numpy()
                 prev = cur
         else:
             for t in range(len(self.my_frames)):
-                _, up = self.ic.step(torch.stack([self.dev_frames[t][0], self.dev_frames[t + 1][0]])[None], crop=self.crop)
-                self.out[t].copy_(up[0])
+                _, up = self.ic.step(torch.stack([self.dev_frames[t][0], self.dev_frames[t + 1][0]])[None])
+                self.out[t].copy_(self._unpad(up)[0])
 
     def gather(self):
         return self.out            # replicas: each rank keeps its own clip's flows

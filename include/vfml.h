@@ -316,6 +316,14 @@ int vfml_motion_glue(const float* fcoords, const float* bcoords, void* x400, int
                      const float* convf1_w, const float* convf1_b, int n_frames, int h, int w,
                      int dtype, vfml_stream_t s);
 
+/* Fused softmax attention of the Twins-SVT stages, fp16, head dimension 32 (LocallyGroupedAttn twins_ft.py:233-261,
+ * GlobalSubSampleAttn :291-312): o[b, i, h, :] = softmax_j(scale * q[b, i, h, :] . k[b, j, h, :]) v[b, j, h, :].
+ * Tensors are addressed as base + b * *_sb + token * *_sn + 32 * h (element strides), so the q / k / v slices of a fused
+ * qkv or kv projection are used in place.  The score matrix is never materialised (online softmax over key blocks). */
+int vfml_attention_hd32(const void* q, const void* k, const void* v, void* o, int n_batch, int n_heads, int n_q, int n_k,
+                        int64_t q_sb, int64_t q_sn, int64_t k_sb, int64_t k_sn, int64_t v_sb, int64_t v_sn, int64_t o_sb,
+                        int64_t o_sn, float scale, vfml_stream_t s);
+
 /* Twins PEG (PosConv, VideoFlow/core/Networks/twins_ft.py:341-355): y = x + dwconv3x3(x) + b on token-major rows
  * [n_img*h*w, C] (fp32 or fp16; C multiple of 4 / 8), weight tap-major [9, C] and bias [C] in the same dtype. */
 int vfml_peg3x3(const void* x, void* y, int n_img, int h, int w, int C, int64_t ld_x, int64_t ld_y, const void* weight,

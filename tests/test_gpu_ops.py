@@ -564,3 +564,22 @@ def test_twins_is_batch_independent():
                 assert torch.isfinite(full).all()
                 for b in (1, 2):
                     assert (enc(x[:b]) - full[:b]).abs().max() <= tol, (H, W, dt, prefix, b)
+
+
+@pytest.mark.parametrize("B,Nq,Nk,heads", [(3, 49, 49, 4), (2, 7040, 416, 8), (1, 1600, 25, 4), (2, 100, 130, 8), (1, 64, 64, 1)])
+def test_attention_hd32_matches_fp64(B, Nq, Nk, heads):
+    """Fused attention kernel (Twins LSA / GSA shapes, ragged key counts, slices of fused projections used in place)."""
+    from video_flow_ml_b200 import ops
+    g = torch.Generator().manual_seed(Nq + Nk)
+    C = heads * 32
+    qkv = (torch.randn((B, Nq, 3 * C), generator=g) * 1.5).half().cuda()
+    kv = (torch.randn((B, Nk, 2 * C), generator=g) * 1.5).half().cuda()
+    q, k, v = qkv[..., C:2 * C], kv[..., 0:C], kv[..., C:2 * C]
+    got = ops.attention_hd32(q, k, v, heads)
+    qd, kd, vd = (t.double().cpu().view(B, -1, heads, 32).transpose(1, 2) for t in (q, k, v))
+    want = (torch.softmax(qd @ kd.transpose(-1, -2) * 32 ** -0.5, -1) @ vd).transpose(1, 2).reshape(B, Nq, C)
+    assert got.shape == (B, Nq, C) and got.dtype == torch.float16
+    err = (got.double().cpu() - want).abs().max().item()
+    assert err <= 4e-3, err
+    with pytest.raises(ValueError):
+        ops.attention_hd32(q.float(), k, v, heads)

@@ -60,6 +60,7 @@ PROTOTYPES = {
     "vfml_dwconv_tc_res_gelu": (i32, [vp, vp, i32, i32, i32, i32, i64, i64, vp, vp, i32, vp]),
     "vfml_splitk_reduce": (i32, [vp, i32, i64, i32, vp, i64, vp, i64, i32, vp]),
     "vfml_layer_norm_rows": (i32, [vp, vp, i64, i32, i64, i64, vp, vp, f32, i32, vp]),
+    "vfml_attention_hd32": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i64, i64, i64, i64, i64, i64, f32, vp]),
     "vfml_peg3x3": (i32, [vp, vp, i32, i32, i32, i32, i64, i64, vp, vp, i32, vp]),
     "vfml_softmax_rows": (i32, [vp, vp, i64, i32, i64, i64, i32, vp]),
     "vfml_motion_glue": (i32, [vp, vp, vp, i64, vp, i64, vp, i64, i32, vp, vp, i32, i32, i32, i32, vp]),

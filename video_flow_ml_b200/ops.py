@@ -566,6 +566,22 @@ def layer_norm_rows(x, weight, bias, eps):
     return y
 
 
+def attention_hd32(q, k, v, n_heads):
+    """Fused attention with head dimension 32 on fp16 CUDA tensors.  q [B, Nq, n_heads*32], k / v [B, Nk, n_heads*32] may be
+    strided views (slices of a fused qkv / kv projection: unit stride along the last axis) -> o [B, Nq, n_heads*32]."""
+    _cuda(q, k, v)
+    B, Nq, Cc = q.shape
+    Nk = k.shape[1]
+    if (Cc != n_heads * 32 or k.shape != (B, Nk, Cc) or v.shape != k.shape or q.dtype != torch.float16 or k.dtype != q.dtype
+            or v.dtype != q.dtype or q.stride(2) != 1 or k.stride(2) != 1 or v.stride(2) != 1):
+        raise ValueError("attention_hd32: expected fp16 [B, N, heads*32] tensors with unit stride along the channels")
+    o = torch.empty((B, Nq, Cc), dtype=torch.float16, device=q.device)
+    _lib.check(_lib.load().vfml_attention_hd32(_p(q), _p(k), _p(v), _p(o), B, n_heads, Nq, Nk, q.stride(0), q.stride(1), k.stride(0),
+                                               k.stride(1), v.stride(0), v.stride(1), o.stride(0), o.stride(1), 32 ** -0.5, _stream()),
+               "attention_hd32")
+    return o
+
+
 def peg3x3(x, n_img, h, w, weight_tapmajor, bias):
     """Twins PEG: x + dwconv3x3(x) + b on a contiguous token-major tensor [n_img, h*w, C]; weight [9, C], same dtype."""
     _cuda(x, weight_tapmajor, bias)

@@ -7,8 +7,8 @@ the reference tree, so the math follows the class definitions vendored in
 VideoFlow/core/Networks/twins_ft.py: PatchEmbed :361-386, LocallyGroupedAttn :214-261,
 GlobalSubSampleAttn :264-312, Block :315-338, PosConv :341-355, svt_large :509-515.
 Weights keep timm's key names (``<prefix>.patch_embeds.0.proj.weight`` ...), so upstream
-checkpoints load unchanged.  LayerNorm and the PEG depthwise convolution are libvfml kernels; the linear layers,
-the strided patch / sub-sampling convolutions and the attention products are library calls (cuBLAS / cuDNN / SDPA).  The
+checkpoints load unchanged.  LayerNorm, the PEG depthwise convolution and (fp16 tier) both attention types are libvfml
+kernels; the linear layers and the strided patch / sub-sampling convolutions are library calls (cuBLAS / cuDNN).  The
 outputs are per-image, so VideoFlowCore.compute_flow_from_frames caches them per frame across sliding windows.
 """
 import torch
@@ -54,9 +54,13 @@ class TwinsStage01:
             x = F.pad(x, (0, 0, 0, pr, 0, pb))
         gh, gw = (H + pb) // _WS, (W + pr) // _WS
         x = x.view(B, gh, _WS, gw, _WS, C).permute(0, 1, 3, 2, 4, 5).reshape(B * gh * gw, _WS * _WS, C)
-        qkv = self._fc(x, name + ".qkv").view(-1, _WS * _WS, 3, heads, C // heads).permute(2, 0, 3, 1, 4)
-        o = F.scaled_dot_product_attention(qkv[0], qkv[1], qkv[2])
-        o = o.transpose(1, 2).reshape(B, gh, gw, _WS, _WS, C).permute(0, 1, 3, 2, 4, 5)
+        qkv = self._fc(x, name + ".qkv")                                        # [windows, 49, 3C]
+        if qkv.is_cuda and qkv.dtype == torch.float16 and C // heads == 32:      # libvfml fused attention on the q / k / v slices in place
+            o = _ops().attention_hd32(qkv[..., 0:C], qkv[..., C:2 * C], qkv[..., 2 * C:3 * C], heads)
+        else:
+            qkv = qkv.view(-1, _WS * _WS, 3, heads, C // heads).permute(2, 0, 3, 1, 4)
+            o = F.scaled_dot_product_attention(qkv[0], qkv[1], qkv[2]).transpose(1, 2)
+        o = o.reshape(B, gh, gw, _WS, _WS, C).permute(0, 1, 3, 2, 4, 5)
         o = o.reshape(B, gh * _WS, gw * _WS, C)[:, :H, :W].reshape(B, N, C)
         return self._fc(o, name + ".proj")
 
@@ -64,14 +68,18 @@ class TwinsStage01:
         """Global attention against keys/values sub-sampled by a strided conv."""
         B, N, C = x.shape
         hd = C // heads
-        q = self._fc(x, name + ".q").view(B, N, heads, hd).transpose(1, 2)
+        q = self._fc(x, name + ".q")
         # .contiguous(): a [1, C, H, W] view of token-major data is stride-ambiguous (NCHW or channels-last); the library's
         # kernel choice for such views has produced wrong results at batch 1 (see ops.peg3x3)
         y = F.conv2d(x.transpose(1, 2).reshape(B, C, H, W).contiguous(), self.p[name + ".sr.weight"], self.p[name + ".sr.bias"], stride=sr)
         y = self._ln(y.flatten(2).transpose(1, 2), name + ".norm", 1e-5)
-        kv = self._fc(y, name + ".kv").view(B, -1, 2, heads, hd).permute(2, 0, 3, 1, 4)
-        o = F.scaled_dot_product_attention(q, kv[0], kv[1])
-        return self._fc(o.transpose(1, 2).reshape(B, N, C), name + ".proj")
+        kv = self._fc(y, name + ".kv")                                           # [B, Nk, 2C]
+        if kv.is_cuda and kv.dtype == torch.float16 and hd == 32:
+            o = _ops().attention_hd32(q, kv[..., 0:C], kv[..., C:2 * C], heads)
+        else:
+            kv = kv.view(B, -1, 2, heads, hd).permute(2, 0, 3, 1, 4)
+            o = F.scaled_dot_product_attention(q.view(B, N, heads, hd).transpose(1, 2), kv[0], kv[1]).transpose(1, 2).reshape(B, N, C)
+        return self._fc(o, name + ".proj")
 
     @torch.no_grad()
     def __call__(self, x):
