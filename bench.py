@@ -569,6 +569,7 @@ def main():
     dev = f"cuda:{local}"
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device(dev))
+        torch.set_num_threads(max(1, host_cores() // world))        # torchrun pins OMP_NUM_THREADS=1: share the host cores instead
     steps = max(args.steps, 1)
     Job = MemFlowJob if cfg["arch"] == "memflow" else FlowJob
     job = Job(cfg, dev, args.precision, iters, world, rank, steps)
