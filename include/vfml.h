@@ -148,6 +148,23 @@ int vfml_corr_lookup_tiled(const void* const* levels_a, const void* const* level
                            void* out_b, int out_pitch, int out_col, int math_f32, vfml_stream_t s);
 
 /* ---------------------------------------------------------------------------------
+ * vfml_corr_volume_pyramid_tiled_static: NO counterpart in the reference; added
+ * for callers that cannot allocate device memory (CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  Same inputs, outputs and results as
+ * vfml_corr_volume_pyramid_tiled, but the workspace is a 16 MiB array built into the library
+ * (vfml_corr_volume_pyramid_tiled_static_max_bytes()); every GPU that loads the library holds
+ * it until the process exits.  The call allocates nothing (no cudaMalloc / cudaFree, no
+ * allocating library routine).  Shapes with vfml_corr_volume_tiled_workspace(n_pairs, C, h, w)
+ * above the maximum return VFML_ERR_WORKSPACE (e.g. C = 256, n_pairs = 1: h*w <= 2651, a
+ * 320 x 512 pixel tile).  All calls on a device share the array: calls that overlap on the GPU
+ * race; order them on one stream or with events.  VFML_ERR_UNSUPPORTED while VFML_GEMM_TRACE is set.
+ * ------------------------------------------------------------------------------- */
+size_t vfml_corr_volume_pyramid_tiled_static_max_bytes(void);
+int vfml_corr_volume_pyramid_tiled_static(const float* fmap1, const float* fmap2, int n_pairs, int C,
+                                          int h, int w, void* const* levels, int num_levels,
+                                          vfml_stream_t s);
+
+/* ---------------------------------------------------------------------------------
  * Convex 8x upsampling (softmax over 9 taps fused).
  * Replaces MOFNet.upsample_flow, MOFNetStack/network.py:97-108.
  *   flow : [n, 2, h, w] fp32;  mask: [n, 576, h, w] fp32 (VFML_NCHW) or rows

@@ -39,6 +39,8 @@ PROTOTYPES = {
     "vfml_corr_tile_pyramid": (i32, [vp, i64, i32, i32, C.POINTER(vp), i32, vp]),
     "vfml_corr_volume_tiled_workspace": (sz, [i32, i32, i32, i32]),
     "vfml_corr_volume_pyramid_tiled": (i32, [vp, vp, i32, i32, i32, i32, C.POINTER(vp), i32, vp, sz, vp]),
+    "vfml_corr_volume_pyramid_tiled_static_max_bytes": (sz, []),
+    "vfml_corr_volume_pyramid_tiled_static": (i32, [vp, vp, i32, i32, i32, i32, C.POINTER(vp), i32, vp]),
     "vfml_corr_lookup_tiled": (i32, [C.POINTER(vp), C.POINTER(vp), i32, i32, i32, vp, vp, vp, vp, i32, i32, i32, vp]),
     "vfml_convex_upsample8": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, i64, i64, i64, i32, i32, i32, i32, i32, vp]),
     "vfml_encode_gamedev": (i32, [vp, vp, i32, i32, f32, f32, f32, f32, vp]),

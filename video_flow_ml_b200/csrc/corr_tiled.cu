@@ -499,3 +499,40 @@ extern "C" int vfml_corr_lookup_tiled(const void* const* levels_a, const void* c
     VFML_LAUNCH_CHECK("corr_lookup_tiled");
     return VFML_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of vfml_corr_volume_pyramid_tiled (no counterpart in the reference; added
+// for callers that cannot allocate: code under CUDA graph capture, tight serving loops, harnesses that
+// forbid cudaMalloc).  The workspace (fp16 rows copies of both feature maps + the level-0 volume) lives in a file-scope
+// device array instead of a caller buffer.  Every GPU that loads the library holds these 16 MiB until the process exits.
+//   * the array's name is only a host-side stand-in here: the device address comes from cudaGetSymbolAddress, once per
+//     device with that device current, and that pointer is what the kernels get;
+//   * nothing in it has to start at zero: the row copies and the volume GEMM overwrite every byte that is read later;
+//   * every call on a device shares the one array: calls that overlap on the GPU (different streams, no dependency) race.
+constexpr size_t STATIC_WS_BYTES = (size_t)16 << 20;
+static __device__ __align__(256) unsigned char g_static_workspace[STATIC_WS_BYTES];
+
+extern "C" size_t vfml_corr_volume_pyramid_tiled_static_max_bytes(void) { return STATIC_WS_BYTES; }
+
+extern "C" int vfml_corr_volume_pyramid_tiled_static(const float* fmap1, const float* fmap2, int n_pairs, int C, int h, int w,
+                                                     void* const* levels, int num_levels, vfml_stream_t s) {
+    VFML_REQUIRE(n_pairs >= 0 && C > 0 && h > 0 && w > 0, "corr_volume_pyramid_tiled_static: bad shape");
+    const size_t need = vfml_corr_volume_tiled_workspace(n_pairs, C, h, w);
+    if (need > STATIC_WS_BYTES) {
+        set_error("corr_volume_pyramid_tiled_static: n_pairs=%d C=%d h=%d w=%d needs %zu bytes of scratch, the built-in array "
+                  "holds %zu; use vfml_corr_volume_pyramid_tiled with a caller workspace", n_pairs, C, h, w, need, STATIC_WS_BYTES);
+        return VFML_ERR_WORKSPACE;
+    }
+    if (getenv("VFML_GEMM_TRACE")) {       // the debug trace of the GEMM allocates its counter buffer
+        set_error("corr_volume_pyramid_tiled_static: not available with VFML_GEMM_TRACE set (the trace buffer is allocated)");
+        return VFML_ERR_UNSUPPORTED;
+    }
+    static PerDevice<void*> addr;
+    void*& ws = addr.get();
+    if (!ws) {
+        void* p = nullptr;
+        VFML_CUDA(cudaGetSymbolAddress(&p, g_static_workspace));
+        ws = p;
+    }
+    return vfml_corr_volume_pyramid_tiled(fmap1, fmap2, n_pairs, C, h, w, levels, num_levels, ws, STATIC_WS_BYTES, s);
+}
