@@ -281,6 +281,12 @@ typedef struct vfml_gemm_desc {
  * GELU + residual chains of PCBlock4_Deep_nopool_res (stack.py:8-32), Attention.to_qk / q.k^T
  * (gma.py:54-74) and Aggregate's attn.v (gma.py:102-115). */
 int vfml_gemm(const vfml_gemm_desc* d, vfml_stream_t s);
+/* Optional, outside CUDA graph capture (it SYNCHRONISES the stream): times the kernels that can run this descriptor -- the
+ * general tcgen05 kernel and the weight-stationary cluster kernel in its single-CTA and CTA-pair modes -- on the caller's
+ * buffers, and makes later vfml_gemm calls of the same (device, M, N, K, epilogue) use the fastest.  Never changes results
+ * beyond fp16 rounding of identical math.  Returns 0 / 1 / 2 (general / cluster single / cluster pair) or a negative
+ * vfml_status; descriptors whose output overlaps an input are left on the general kernel.  Same reference code as vfml_gemm. */
+int vfml_gemm_autotune(const vfml_gemm_desc* d, vfml_stream_t s);
 /* 1 if vfml_gemm would run this descriptor on the tcgen05 tensor-core kernel (fp16 operands, 16-byte
  * aligned bases and pitches), 0 if on the exact fp32 FFMA kernel. */
 int vfml_gemm_uses_tensor_cores(const vfml_gemm_desc* d);

@@ -41,6 +41,12 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n.reg .pred P;\nelect.sync _|P, 0xFFFFFFFF;\nselp.b32 %0, 1, 0, P;\n}\n" : "=r"(pred));
+    return pred != 0;
+}
+
 constexpr int MAX_STAGES = 8;
 
 __global__ void __launch_bounds__(320, 1) probe(int N, int iters, int stages, int mode, int fill, int kb_per_tile, long long* out) {
@@ -85,6 +91,34 @@ __global__ void __launch_bounds__(320, 1) probe(int N, int iters, int stages, in
                 mbar_arrive(&full_bar[s]);
             }
         }
+    } else if (warp == 1 && (mode & 32)) {
+        // the kernels' style: the whole warp runs the loop (addresses and counters stay warp-uniform), only the issue is elected;
+        // mode bit 6: the K=16 steps of TWO k-blocks issued back to back before their two commits
+        const uint32_t idesc = (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        const long long t0 = clock64();
+        int s = 0, kb = 0;
+        uint32_t ph = 0, buf = 0;
+        const uint64_t ad0 = make_sw128_desc(smem_u32(smem)), bd0 = make_sw128_desc(smem_u32(smem + (size_t)stages * a_bytes));
+        const uint64_t a_step = a_bytes >> 4, b_step = b_bytes >> 4;
+        uint64_t ad = ad0, bd = bd0;
+        for (int it = 0; it < iters; ++it) {
+            if (mode & 2) mbar_wait(&full_bar[s], ph);
+            if (mode & 4) asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (elect_one()) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_f16(tmem + buf * 256u, ad + k * 2, bd + k * 2, idesc, (kb | k) ? 1u : 0u);
+                if (mode & 1) umma_commit(&empty_bar[s]);
+            }
+            __syncwarp();
+            ad += a_step; bd += b_step;
+            if (++s == stages) { s = 0; ph ^= 1u; ad = ad0; bd = bd0; }
+            if (++kb == kb_per_tile) { kb = 0; buf ^= 1u; }
+        }
+        if (elect_one()) umma_commit(&done_bar);
+        __syncwarp();
+        mbar_wait(&done_bar, 0);
+        const long long t1 = clock64();
+        if (blockIdx.x == 0 && lane == 0) out[0] = t1 - t0;
     } else if (warp == 1) {
         if (lane == 0) {
             const uint32_t idesc = (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
@@ -132,8 +166,8 @@ int main() {
     const int iters = 4000;
     printf("128 x N x 64 k-blocks (4 MMAs of K=16 each), %d k-blocks, 6 per tile, grid 148; ideal = N/2 cycles per MMA\n", iters);
     for (int fill = 1; fill < 2; ++fill)
-        for (int mode : {0, 16, 7, 23, 31})
-            for (int N : {128, 160, 176, 256}) {
+        for (int mode : {16, 23, 32, 33, 39})
+            for (int N : {64, 96, 128, 160, 176, 256}) {
                 const int stages = 4;
                 const size_t smem = 1024 + stages * (128 * 128 + N * 128);
                 float ms = 0;

@@ -125,6 +125,16 @@ def dwconv_res_gelu(x, y, n_img, h, w, weight_tapmajor, bias, k):
     return y
 
 
+class gemm_autotuning:
+    """no-op stand-in for ops.gemm_autotuning (kernel selection has no CPU counterpart)"""
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+
 def gemm_splitk(a, w, out, n_splits, partial, res=None, alpha=1.0):
     Ks = a.shape[1] // n_splits
     acc = torch.zeros(out.shape, dtype=torch.float32)

@@ -261,6 +261,44 @@ def test_gemm_tensor_core(ops, M, N, K):
             close(got, want, 2e-3, 2e-3)
 
 
+@pytest.mark.parametrize("pair,cs", [(0, 1), (0, 2), (0, 4), (0, 8), (1, 2), (1, 4), (1, 8)])
+@pytest.mark.parametrize("M,N,K", [(1408, 486, 324), (1300, 324, 486), (2176, 768, 512), (640, 128, 128), (1100, 600, 400), (900, 172, 600),
+                                   (777, 193, 100), (512, 20, 64)])
+def test_gemm_weight_stationary_cluster_sizes(ops, monkeypatch, pair, cs, M, N, K):
+    """gemm_ws.cu with the mode (single CTAs / tcgen05 CTA pairs) and the cluster size pinned: multicast of A, the pair's
+    relay and remote accumulator hand-back, TMA residual load / in-place update / TMA store, ragged last row tile (pair
+    mode: a whole CTA of the last tile is out of range), column tiles that end inside a 32-column box, views into wider buffers."""
+    monkeypatch.setenv("VFML_WS_CS", str(cs))
+    monkeypatch.setenv("VFML_WS_PAIR", str(pair))
+    r = torch.Generator().manual_seed(M + 3 * N + 7 * K + cs)
+    a = torch.randn((M, K), generator=r).half()
+    w = (torch.randn((N, K), generator=r) / K ** 0.5).half()
+    bias, dww, dwb = torch.randn(N, generator=r), torch.randn(N, generator=r) * 0.3, torch.randn(N, generator=r) * 0.3
+    res = torch.randn((M, N), generator=r).half()
+    A, Wt = _aligned(a), _aligned(w)
+    A.as_strided((M, A.stride(0) - K), (A.stride(0), 1), A.storage_offset() + K).fill_(50.0)       # poisoned row padding: the K tail
+    Wt.as_strided((N, Wt.stride(0) - K), (Wt.stride(0), 1), Wt.storage_offset() + K).fill_(50.0)   # must come from TMA's zero fill
+    wide = torch.full((M, 2 * ((N + 7) // 8 * 8) + 24), 7.0, dtype=torch.float16, device="cuda")
+    R = wide[:, 8:8 + N]
+    R.copy_(res)
+    for kw in (dict(), dict(bias=bias), dict(bias=bias, act="gelu"), dict(bias=bias, res=res), dict(bias=bias, res=res, act="gelu"),
+               dict(bias=bias, res=res, act="gelu", dw=(dww, dwb))):
+        want = torch.zeros((M, N), dtype=torch.float32)
+        fake_ops.gemm(a, w, want, **kw)
+        kwc = {k: (tuple(cu(x) for x in v) if isinstance(v, tuple) else v) for k, v in kw.items()}
+        if "bias" in kwc:
+            kwc["bias"] = cu(bias)
+        if "res" in kwc:
+            kwc["res"] = R
+        off = 8 + (N + 7) // 8 * 8 + 8
+        got = wide[:, off:off + N]
+        got.fill_(-3.0)
+        ops.gemm(A, Wt, got, require_tc=True, **kwc)
+        close(got, want, 2e-3, 2e-3)
+        close(R, res, 0)                                          # the residual is untouched
+        assert float(wide[:, off + N:].float().sub(7.0).abs().max()) == 0 and float(wide[:, 8 + N:off].float().sub(7.0).abs().max()) == 0
+
+
 def test_gemm_tensor_core_large_k_and_strided_views(ops):
     """attention-shaped products: K = 7040 (110 k-blocks through the stage ring), operands that are column
     slices of wider buffers."""

@@ -22,6 +22,7 @@
 
 #include "common.cuh"
 #include "gelu_poly.cuh"
+#include "tcgen05.cuh"
 
 namespace vfml {
 
@@ -57,151 +58,6 @@ struct TcParams {
     int b_is_const;      // B (and bias / dw vectors) are weights: may be fetched before the preceding kernel has finished
     long long* trace;    // debug (VFML_GEMM_TRACE=1): per-CTA cycle counters, 16 per CTA
 };
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_LOOP:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra WAIT_DONE;\n"
-        "bra WAIT_LOOP;\n"
-        "WAIT_DONE:\n"
-        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void tma_load_3d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1, int c2) {
-    asm volatile(
-        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
-}
-__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
-        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
-}
-// one lane of a converged warp (the same lane every time for a full mask).  The producer and MMA warps run their loops with
-// all 32 lanes and predicate only the issue on this: addresses, descriptors and ring counters then stay warp-uniform, the
-// compiler keeps them in uniform registers, and UTMALDG / UTCHMMA / UTCBAR take them directly.  Under `if (lane == 0)` the
-// same values count as divergent and every such instruction is wrapped in an ELECT / R2UR.BROADCAST / BRA.U.ANY
-// uniformisation loop: ~100 cycles of single-thread issue latency per MMA, more than a 128 x 176 x 16 MMA executes in.
-__device__ __forceinline__ bool elect_one() {
-    uint32_t pred;
-    asm volatile("{\n.reg .pred P;\nelect.sync _|P, 0xFFFFFFFF;\nselp.b32 %0, 1, 0, P;\n}\n" : "=r"(pred));
-    return pred != 0;
-}
-__device__ __forceinline__ void st_global_256(void* ptr, const uint4& a, const uint4& b) {
-    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
-                 ::"l"(ptr), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w) : "memory");
-}
-__device__ __forceinline__ void ld_global_256(const void* ptr, uint4& a, uint4& b) {
-    asm volatile("ld.global.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
-                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w) : "l"(ptr));
-}
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
-    uint32_t r[16];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-__device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&r)[16]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr));
-}
-// the registers of an issued tcgen05.ld may only be read after this wait; they are passed through the
-// asm statement so that the compiler cannot hoist their uses above it
-__device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[16]) {
-    asm volatile("tcgen05.wait::ld.sync.aligned;"
-                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
-                   "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
-                 :: "memory");
-}
-
-
-// tcgen05.ld shape 16x256b, 8 repetitions: 16 TMEM lanes (rows) x 64 fp32 columns.  Thread t of the warp receives, for
-// every 8-column group g, r[4g + {0,1}] = row t / 4, columns 8g + 2 (t % 4) + {0,1} and r[4g + {2,3}] = row t / 4 + 8, same
-// columns (the mma C-fragment arrangement): the four lanes of a quad hold one row segment between them.
-__device__ __forceinline__ void tmem_ld_16x256b_x8_issue(uint32_t taddr, uint32_t (&r)[32]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.16x256b.x8.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
-          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
-          "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
-          "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-        : "r"(taddr));
-}
-__device__ __forceinline__ void tmem_ld_wait32(uint32_t (&r)[32]) {
-    asm volatile("tcgen05.wait::ld.sync.aligned;"
-                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]),
-                   "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]), "+r"(r[16]), "+r"(r[17]), "+r"(r[18]),
-                   "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]),
-                   "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
-                 :: "memory");
-}
-// 4 x 4 transpose of 32-bit words across the lanes of a quad: lane q passes row q of a matrix and receives column q.
-__device__ __forceinline__ void quad_transpose4(uint32_t& a0, uint32_t& a1, uint32_t& a2, uint32_t& a3, int q) {
-    const bool o1 = q & 1, o2 = q & 2;
-    uint32_t x0 = o1 ? a0 : a1, x1 = o1 ? a2 : a3;
-    x0 = __shfl_xor_sync(0xffffffffu, x0, 1);
-    x1 = __shfl_xor_sync(0xffffffffu, x1, 1);
-    if (o1) { a0 = x0; a2 = x1; } else { a1 = x0; a3 = x1; }
-    x0 = o2 ? a0 : a2; x1 = o2 ? a1 : a3;
-    x0 = __shfl_xor_sync(0xffffffffu, x0, 2);
-    x1 = __shfl_xor_sync(0xffffffffu, x1, 2);
-    if (o2) { a0 = x0; a1 = x1; } else { a2 = x0; a3 = x1; }
-}
-// Row-contiguous words R[k] (lane q of the quad holds columns 16 q + 2 k, + 1 of a 64-column row segment, k = 0..7)  <->
-// fragment words F[g] (columns 8 g + 2 q, + 1): R[4 b + j] = F_lane j [2 s + b] for lane s, i.e. two quad transposes.
-__device__ __forceinline__ void quad_frag_to_rows(uint32_t (&w)[8], int q) {
-    quad_transpose4(w[0], w[2], w[4], w[6], q);      // b = 0: F[0], F[2], F[4], F[6] -> R[0..3]
-    quad_transpose4(w[1], w[3], w[5], w[7], q);      // b = 1: F[1], F[3], F[5], F[7] -> R[4..7]
-    const uint32_t r1 = w[2], r2 = w[4], r3 = w[6], r4 = w[1], r5 = w[3], r6 = w[5];
-    w[1] = r1; w[2] = r2; w[3] = r3; w[4] = r4; w[5] = r5; w[6] = r6;
-}
-__device__ __forceinline__ void quad_rows_to_frag(uint32_t (&w)[8], int q) {
-    uint32_t a0 = w[0], a1 = w[1], a2 = w[2], a3 = w[3], b0 = w[4], b1 = w[5], b2 = w[6], b3 = w[7];
-    quad_transpose4(a0, a1, a2, a3, q);              // -> F[0], F[2], F[4], F[6]
-    quad_transpose4(b0, b1, b2, b3, q);              // -> F[1], F[3], F[5], F[7]
-    w[0] = a0; w[2] = a1; w[4] = a2; w[6] = a3; w[1] = b0; w[3] = b1; w[5] = b2; w[7] = b3;
-}
-
-// shared-memory matrix descriptor, K-major, 128-byte swizzle: 8-row groups of 128 B rows, 1024 B apart
-__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr >> 4) & 0x3FFF);          // start address
-    d |= (uint64_t)1 << 16;                          // leading byte offset (unused for swizzled K-major)
-    d |= (uint64_t)(1024 >> 4) << 32;                // stride byte offset between 8-row groups
-    d |= (uint64_t)1 << 46;                          // descriptor version (Blackwell)
-    d |= (uint64_t)2 << 61;                          // SWIZZLE_128B
-    return d;
-}
 
 // SPEC >= 0: the epilogue flag set (a subset of BIAS | RES | GELU | DW1) is a compile-time constant, the output is fp16,
 // alpha == 1 and the per-column vectors are in shared memory: the per-chunk epilogue becomes one basic block (no uniform

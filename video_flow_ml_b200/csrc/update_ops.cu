@@ -371,6 +371,10 @@ int dwconv_tiled(const void* x, void* y, int n_img, int h, int w, int C, int64_t
 int gemm_ffma(const vfml_gemm_desc& d, cudaStream_t st);
 int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st);
 bool gemm_tc_supported(const vfml_gemm_desc& d);
+int gemm_ws(const vfml_gemm_desc& d, cudaStream_t st, int mode);
+bool gemm_ws_supported(const vfml_gemm_desc& d);
+int gemm_ws_choice(const vfml_gemm_desc& d);
+int gemm_autotune(const vfml_gemm_desc& d, cudaStream_t st);
 int validate_gemm(const vfml_gemm_desc* d);
 
 }  // namespace vfml
@@ -415,8 +419,22 @@ extern "C" int vfml_gemm(const vfml_gemm_desc* d, vfml_stream_t s) {
     if (d->M == 0 || d->N == 0) return VFML_OK;
     // fp16 operands with TMA-compatible alignment -> tcgen05 tensor-core kernel; fp32 (exact tier) and
     // oddly aligned fp16 views -> FFMA kernel.  Both are libvfml kernels with identical semantics.
+    if (gemm_ws_supported(*d)) {           // the update block's big pointwise layers: the cluster kernel where it measured faster
+        const int choice = gemm_ws_choice(*d);          // 0: gemm_tc (also: never tuned), 1 / 2: gemm_ws single / pair, -1: pinned by the environment
+        if (choice != 0) {
+            rc = gemm_ws(*d, to_stream(s), choice < 0 ? -1 : choice - 1);
+            if (rc <= 0) return rc;        // > 0: declined (weight slice does not fit), fall through
+        }
+    }
     if (gemm_tc_supported(*d)) return gemm_tc(*d, to_stream(s));
     return gemm_ffma(*d, to_stream(s));
+}
+
+extern "C" int vfml_gemm_autotune(const vfml_gemm_desc* d, vfml_stream_t s) {
+    int rc = validate_gemm(d);
+    if (rc) return rc;
+    if (d->M == 0 || d->N == 0) return 0;
+    return gemm_autotune(*d, to_stream(s));
 }
 
 extern "C" int vfml_dwconv_res_gelu(const void* x, void* y, int n_img, int h, int w, int C, int64_t pitch_x,

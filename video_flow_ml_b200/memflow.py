@@ -227,7 +227,8 @@ class MemFlowEngine(MOFEngine):
         g = ws["graphs"].get(key)
         if g is None:
             static = [t.clone() for t in args]
-            self._body(ws, *static, h, w, self.n_stored)            # eager warm-up; only the current-frame memory slot is written
+            with _ops.gemm_autotuning():
+                self._body(ws, *static, h, w, self.n_stored)            # eager warm-up; only the current-frame memory slot is written
             torch.cuda.synchronize(self.dev)
             graph = torch.cuda.CUDAGraph()
             n0 = _lib.launch_count()

@@ -489,7 +489,8 @@ class MOFEngine:
             static = [torch.empty_like(t) for t in (fmaps, net, inp)]
             for s_, t in zip(static, (fmaps, net, inp)):
                 s_.copy_(t)
-            self._iterations_body(ws, *static, Fc, h, w, iters=1)   # eager warm-up (one iteration reaches every kernel): module
+            with _ops.gemm_autotuning():                            # each layer shape picks its GEMM kernel by measurement, once
+                self._iterations_body(ws, *static, Fc, h, w, iters=1)   # eager warm-up (one iteration reaches every kernel): module
             torch.cuda.synchronize(self.dev)                        # loading and one-time attributes cannot happen under capture
             graph = torch.cuda.CUDAGraph()
             n0 = _lib.launch_count()

@@ -7,6 +7,8 @@ streams only; every function launches libvfml kernels on the current CUDA stream
 import ctypes as C
 import functools
 
+import os
+
 import torch
 
 from . import _lib
@@ -466,8 +468,29 @@ def gemm(a, w, out, bias=None, res=None, act=None, dw=None, alpha=1.0, addto=Fal
     d.in_dtype, d.out_dtype = _dt(a), _dt(out)
     if require_tc and not _lib.load().vfml_gemm_uses_tensor_cores(C.byref(d)):
         raise RuntimeError("gemm: descriptor is not eligible for the tensor-core kernel (alignment / dtype)")
+    if _GEMM_AUTOTUNE[0] and a.dtype == torch.float16:
+        rc = _lib.load().vfml_gemm_autotune(C.byref(d), _stream())
+        if rc < 0:
+            _lib.check(rc, "gemm_autotune")
     _lib.check(_lib.load().vfml_gemm(C.byref(d), _stream()), "gemm")
     return out
+
+
+_GEMM_AUTOTUNE = [False]
+
+
+class gemm_autotuning:
+    """with ops.gemm_autotuning(): ...   every ops.gemm inside first lets the library time its kernels for that layer shape
+    (vfml_gemm_autotune: synchronises, so only outside graph capture -- the engines use it around their eager warm-up)."""
+
+    def __enter__(self):
+        self.prev = _GEMM_AUTOTUNE[0]
+        _GEMM_AUTOTUNE[0] = os.environ.get("VFML_GEMM_NO_AUTOTUNE") is None
+        return self
+
+    def __exit__(self, *exc):
+        _GEMM_AUTOTUNE[0] = self.prev
+        return False
 
 
 def gemm_batched(a, b, out, alpha=1.0):
