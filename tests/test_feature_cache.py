@@ -24,7 +24,7 @@ class StubEngine:
     def encode_new_frames(self, xf, xc):
         return (None if xf is None else self.encode_frames(xf)), (None if xc is None else self.encode_frames(xc, context=True))
 
-    def refine(self, fmaps, net, inp, select=None, crop=None, out=None):
+    def refine(self, fmaps, net, inp, select=None, crop=None, out=None, frame_keys=None):
         self.last = (fmaps[:, 0, 0, 0].clone(), net[:, 0, 0, 0].clone(), inp[:, 0, 0, 0].clone(), select, crop)
         return torch.zeros(2, crop[2], crop[3])
 

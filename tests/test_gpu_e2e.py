@@ -387,6 +387,37 @@ def test_feature_cache_equals_uncached_and_saves_encoder_passes():
     assert p.core.cache_stats["fnet_runs"] == before["fnet_runs"] + 1 and p.core.cache_stats["cnet_runs"] == before["cnet_runs"] + 1
 
 
+def test_pyramid_reuse_between_sliding_windows_is_bit_exact():
+    """A window that follows its predecessor by one frame re-uses the correlation pyramids of the shared centre frames
+    (slot copies + one new pair instead of 2 (T-2) pairs, a second CUDA graph): bit-identical flows with and without
+    (same call sequence, so the per-frame encoder cache behaves identically in both runs), also across jumps in the clip
+    (re-use must not trigger) and after an in-place edit of a shared frame (its pairs are rebuilt)."""
+    sd = omof.mof_synthetic_weights(0, gain=1.0)
+    orig = [f.astype(np.float32) for f in cases.mof_case(seed=77, n_frames=11)]
+    order = [2, 3, 4, 5, 8, 9, 3, 4]                 # slides, a jump, a slide, a jump back, a slide
+
+    def run(cache):
+        frames = [f.copy() for f in orig]
+        p = _proc("fp16", sd, iters=3)
+        eng = p.core.model
+        assert eng.tiled
+        eng.pyramid_cache = cache
+        got = [p.compute_optical_flow(frames, i) for i in order]
+        slides = [eng.pyramid_slides]                               # windows 3, 4, 5 | 9 | 4
+        frames[6][:] = frames[6][:, ::-1].copy()                    # frame 6 is in two pairs the window at 5 would have re-used
+        got.append(p.compute_optical_flow(frames, 5))
+        slides.append(eng.pyramid_slides)
+        got.append(p.compute_optical_flow(frames, 6))
+        slides.append(eng.pyramid_slides)
+        return got, slides
+
+    got, slides = run(True)
+    want, none = run(False)
+    assert slides == [5, 5, 6] and none == [0, 0, 0], (slides, none)
+    for k, (a, b) in enumerate(zip(want, got)):
+        assert np.array_equal(a, b), (k, float(np.abs(a - b).max()))
+
+
 def test_device_resident_post_pass_matches_reference_golden(golden):
     """SURVEY 8(f) n2 against the REFERENCE's outputs (post.npz), not against this repo's host path: the device-resident
     encode and TAA (CUDA tensors in, CUDA tensors out, no host hop) reproduce the reference encoders bit for bit and

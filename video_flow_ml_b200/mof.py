@@ -137,6 +137,9 @@ class MOFEngine:
         self.vol_dtype = None            # untiled tiers only: storage type of the volume (default: the tier's dtype)
         self.lookup_math_f32 = False     # fp16x2 interpolation: 2.43e-2 px vs 2.37e-2 px (fp32) end to end, 8 % faster
         self.graph_launches = 0          # kernels executed through CUDA-graph replays (not seen by vfml_launch_count)
+        # re-use of correlation pyramids between consecutive sliding windows (refine(frame_keys=...)); VFML_PYRAMID_CACHE=0 disables
+        self.pyramid_cache = os.environ.get("VFML_PYRAMID_CACHE", "1") != "0"
+        self.pyramid_slides = 0          # windows that re-used their predecessor's pyramids
         self.use_side_stream = os.environ.get("VFML_NO_SIDE_STREAM") is None
 
     # ------------------------------------------------------------------ buffers
@@ -364,9 +367,26 @@ class MOFEngine:
             fm, ctx = g["out"]       # static outputs: the cache keeps copies
             return (None if fm is None else fm.clone()), (None if ctx is None else (ctx[0].clone(), ctx[1].clone()))
 
-    def build_pyramids(self, fmaps, ws=None):
-        """Forward (frames 1..T-2 vs 2..T-1) and backward (vs 0..T-3) pyramids, network.py:157-158."""
+    def build_pyramids(self, fmaps, ws=None, slide=False):
+        """Forward (frames 1..T-2 vs 2..T-1) and backward (vs 0..T-3) pyramids, network.py:157-158.
+        slide=True (tiled pyramids kept in the workspace): the previous window was this one shifted by one frame, so its
+        pyramids of centre frames 1.. ARE this window's pyramids of centre frames 0.. (a correlation pyramid depends on its
+        two frames only): they move down one slot (device copies, 4x cheaper than the volume GEMM + pooling) and only the
+        last centre frame's pair is computed."""
         T = fmaps.shape[0]
+        if slide:
+            Fc = T - 2
+            fp, bp = ws["fpyr"], ws["bpyr"]
+            P = fp.h * fp.w
+            for pyr in (fp, bp):
+                for lv in pyr.levels:
+                    for j in range(Fc - 1):          # ascending: slot j is free once it has been copied to j - 1
+                        lv[j * P:(j + 1) * P].copy_(lv[(j + 1) * P:(j + 2) * P])
+            last = lambda pyr: self.ops.TiledPyramid([lv[(Fc - 1) * P:Fc * P] for lv in pyr.levels], 1, pyr.h, pyr.w)
+            c1 = fmaps[T - 2:T - 1].contiguous()
+            self.ops.corr_volume_pyramid_tiled(c1, fmaps[T - 1:T].contiguous(), ws.get("vol_ws"), out=last(fp))
+            self.ops.corr_volume_pyramid_tiled(c1, fmaps[T - 3:T - 2].contiguous(), ws.get("vol_ws"), out=last(bp))
+            return fp, bp
         c = fmaps[1:T - 1].contiguous()
         if self.tiled:
             ws = ws or {}
@@ -461,11 +481,11 @@ class MOFEngine:
         d = direction if self.arch == "mof" else 1 - direction
         return slice(576 * d, 576 * (d + 1))
 
-    def _iterations_body(self, ws, fmaps, net, inp, Fc, h, w, iters=None):
+    def _iterations_body(self, ws, fmaps, net, inp, Fc, h, w, iters=None, slide=False):
         """pyramids, attention, `iters` update steps.  Leaves net in x512[:, 0:128]; returns the coords."""
         o = self.ops
         P = h * w
-        fpyr, bpyr = self.build_pyramids(fmaps, ws)
+        fpyr, bpyr = self.build_pyramids(fmaps, ws, slide=slide)
         x512 = ws["x512"]
         o.nchw_to_rows(net, x512[:, 0:128])
         o.nchw_to_rows(inp, x512[:, 128:256])
@@ -478,47 +498,70 @@ class MOFEngine:
             self.update_step(ws, fpyr, bpyr, fc, bc, Fc, h, w)
         return fc, bc
 
-    def _run_iterations(self, ws, fmaps, net, inp, Fc, h, w):
+    @staticmethod
+    def _pair_keys(frame_keys, Fc):
+        """identity of every pyramid of a window: (centre frame, partner frame) per slot, forward then backward"""
+        if frame_keys is None or any(k is None for k in frame_keys):
+            return None
+        k = list(frame_keys)
+        return tuple((k[j + 1], k[j + 2]) for j in range(Fc)) + tuple((k[j + 1], k[j]) for j in range(Fc))
+
+    def _run_iterations(self, ws, fmaps, net, inp, Fc, h, w, frame_keys=None):
         """The ~1300 launches of a window are captured once per shape into a CUDA graph and replayed
-        (inputs are copied into static buffers; the graph owns the pyramids and the coords)."""
+        (inputs are copied into static buffers; the graph owns the pyramids and the coords).  A second graph per shape
+        serves windows that follow their predecessor by one frame (frame_keys: hashable identities of the T frames, the
+        same keys as the per-frame feature cache): it re-uses the pyramids of the shared centre frames (build_pyramids)."""
         fmaps, net, inp = fmaps.float().contiguous(), net.float().contiguous(), inp.float().contiguous()
+        pairs = self._pair_keys(frame_keys, Fc) if (self.tiled and self.pyramid_cache and Fc > 1) else None
+        prev = ws.get("pyr_keys")
+        slide = (pairs is not None and prev is not None
+                 and all(pairs[j] == prev[j + 1] and pairs[Fc + j] == prev[Fc + j + 1] for j in range(Fc - 1)))
+        ws["pyr_keys"] = None                      # (stays None if anything below raises: the slots are then in an unknown state)
         if not (self.use_graph and fmaps.is_cuda):
-            return self._iterations_body(ws, fmaps, net, inp, Fc, h, w)
-        g = ws.get("graph")
+            out = self._iterations_body(ws, fmaps, net, inp, Fc, h, w, slide=slide)
+            ws["pyr_keys"] = pairs
+            self.pyramid_slides += int(slide)
+            return out
+        graphs = ws.setdefault("graphs", {})
+        g = graphs.get(slide)
         if g is None or g["iters"] != self.iters:
             static = [torch.empty_like(t) for t in (fmaps, net, inp)]
             for s_, t in zip(static, (fmaps, net, inp)):
                 s_.copy_(t)
-            with _ops.gemm_autotuning():                            # each layer shape picks its GEMM kernel by measurement, once
-                self._iterations_body(ws, *static, Fc, h, w, iters=1)   # eager warm-up (one iteration reaches every kernel): module
+            if not graphs:
+                with _ops.gemm_autotuning():                            # each layer shape picks its GEMM kernel by measurement, once
+                    self._iterations_body(ws, *static, Fc, h, w, iters=1)   # eager warm-up (one iteration reaches every kernel): module
             torch.cuda.synchronize(self.dev)                        # loading and one-time attributes cannot happen under capture
+            # (a first slide-graph capture leaves the previous window's pyramids in place: capturing records, it does not run)
             graph = torch.cuda.CUDAGraph()
             n0 = _lib.launch_count()
             with torch.cuda.graph(graph):
-                coords = self._iterations_body(ws, *static, Fc, h, w)
-            g = ws["graph"] = {"graph": graph, "static": static, "coords": coords, "iters": self.iters,
-                               "launches": _lib.launch_count() - n0}
+                coords = self._iterations_body(ws, *static, Fc, h, w, slide=slide)
+            g = graphs[slide] = {"graph": graph, "static": static, "coords": coords, "iters": self.iters,
+                                 "launches": _lib.launch_count() - n0}
         for s_, t in zip(g["static"], (fmaps, net, inp)):
             s_.copy_(t)
         g["graph"].replay()
+        ws["pyr_keys"] = pairs
+        self.pyramid_slides += int(slide)
         self.graph_launches += g["launches"]
         return g["coords"]
 
     # ------------------------------------------------------------------ forward
     @torch.no_grad()
-    def refine(self, fmaps, net, inp, select=None, crop=None, out=None):
+    def refine(self, fmaps, net, inp, select=None, crop=None, out=None, frame_keys=None):
         """fmaps [T,256,h,w], net/inp [T-2,128,h,w] (fp32, CUDA).
         select=None  -> all flows [1, 2(T-2), 2, 8h, 8w] (forward flows then backward), network.py:210-215
         select=index -> only that flow [2, out_h, out_w]; crop=(top, left, out_h, out_w) fuses the unpad."""
         with self._guard():
-            return self._refine(fmaps, net, inp, select, crop, out)
+            return self._refine(fmaps, net, inp, select, crop, out, frame_keys)
 
-    def _refine(self, fmaps, net, inp, select, crop, out):
+    def _refine(self, fmaps, net, inp, select, crop, out, frame_keys=None):
         o = self.ops
         T, _, h, w = fmaps.shape
         Fc, P = T - 2, h * w
         ws = self._workspace(Fc, h, w)
-        fc, bc = self._run_iterations(ws, fmaps, net, inp, Fc, h, w)
+        fc, bc = self._run_iterations(ws, fmaps, net, inp, Fc, h, w, frame_keys)
         if select is None:
             flows = torch.empty((1, 2 * Fc, 2, 8 * h, 8 * w), dtype=torch.float32, device=self.dev)
             mk = self.mask_rows(ws, slice(0, Fc), h, w, self._mask_chan(0))

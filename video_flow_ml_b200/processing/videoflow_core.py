@@ -181,7 +181,7 @@ class VideoFlowCore:
             fmaps = torch.stack([e["fmap"] for e in ent])
             net = torch.stack([ent[i]["ctx"][0] for i in centre])
             inp = torch.stack([ent[i]["ctx"][1] for i in centre])
-            return self.model.refine(fmaps, net, inp, select=Tn - 2, crop=(tp, l, H, W), out=out)
+            return self.model.refine(fmaps, net, inp, select=Tn - 2, crop=(tp, l, H, W), out=out, frame_keys=keys)
 
     def clear_feature_cache(self):
         self._feat.clear()

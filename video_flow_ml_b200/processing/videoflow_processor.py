@@ -106,10 +106,12 @@ class VideoFlowProcessor:
 
     @staticmethod
     def _frame_key(f):
-        """Identity of a frame array: address, layout, and 4 KB of strided content (an in-place edit of the array is
-        noticed unless it misses every sampled byte; callers that do that should disable the cache)."""
-        flat = f.reshape(-1).view(np.uint8) if f.flags.c_contiguous else np.ascontiguousarray(f).reshape(-1).view(np.uint8)
-        step = max(1, flat.size // 4096)
+        """Identity of a frame array: address, layout, and ~4096 strided ELEMENTS of content (an in-place edit of the array
+        is noticed unless it misses every sampled element; callers that do that should disable the cache).  Whole elements at
+        an odd stride: a byte stride that is a multiple of the item size would only ever see, e.g., the always-zero low
+        mantissa byte of integer-valued float32 frames, and an even one only one colour channel."""
+        flat = f.reshape(-1) if f.flags.c_contiguous else np.ascontiguousarray(f).reshape(-1)
+        step = max(1, flat.size // 4096) | 1
         return (f.__array_interface__['data'][0], f.shape, f.dtype.str, f.strides, hash(flat[::step].tobytes()))
 
     def _device_frame(self, f, key):
