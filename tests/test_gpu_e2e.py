@@ -366,6 +366,7 @@ def test_feature_cache_equals_uncached_and_saves_encoder_passes():
     one new cnet pass per steady-state window."""
     sd = omof.mof_synthetic_weights(0, gain=1.0)
     p = _proc("fp32", sd, iters=4)
+    p.core.prefetch = False          # (the prefetch of the next window's frame would add its encoder passes to the counts)
     frames = [np.clip(f, 0, 255).astype(np.uint8) for f in cases.mof_case(seed=31, n_frames=8)]
     got = [p.compute_optical_flow(frames, i) for i in range(2, 6)]
     st = dict(p.core.cache_stats)
@@ -396,11 +397,12 @@ def test_pyramid_reuse_between_sliding_windows_is_bit_exact():
     orig = [f.astype(np.float32) for f in cases.mof_case(seed=77, n_frames=11)]
     order = [2, 3, 4, 5, 8, 9, 3, 4]                 # slides, a jump, a slide, a jump back, a slide
 
-    def run(cache):
+    def run(cache, prefetch=True):
         frames = [f.copy() for f in orig]
         p = _proc("fp16", sd, iters=3)
         eng = p.core.model
-        assert eng.tiled
+        assert eng.tiled and p.core.prefetch
+        p.core.prefetch = prefetch
         eng.pyramid_cache = cache
         got = [p.compute_optical_flow(frames, i) for i in order]
         slides = [eng.pyramid_slides]                               # windows 3, 4, 5 | 9 | 4
@@ -416,6 +418,10 @@ def test_pyramid_reuse_between_sliding_windows_is_bit_exact():
     assert slides == [5, 5, 6] and none == [0, 0, 0], (slides, none)
     for k, (a, b) in enumerate(zip(want, got)):
         assert np.array_equal(a, b), (k, float(np.abs(a - b).max()))
+    # the encoder prefetch of the next window's new frame (side stream, beside the iterations) changes nothing either
+    plain, _ = run(False, prefetch=False)
+    for k, (a, b) in enumerate(zip(plain, got)):
+        assert np.array_equal(a, b), ("prefetch", k, float(np.abs(a - b).max()))
 
 
 def test_device_resident_post_pass_matches_reference_golden(golden):

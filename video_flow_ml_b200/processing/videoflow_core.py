@@ -45,6 +45,10 @@ class VideoFlowCore:
         self.feature_cache_frames = int(os.environ.get("VFML_FEATURE_CACHE", "96"))
         self._feat = collections.OrderedDict()        # key -> {"fmap": [256,h,w], "ctx": (net, inp) or None}
         self.cache_stats = {"fnet_runs": 0, "cnet_runs": 0, "fnet_hits": 0, "cnet_hits": 0}
+        # encoder outputs of the NEXT window computed on a side stream while the current one iterates (VFML_PREFETCH=0 disables)
+        self.prefetch = os.environ.get("VFML_PREFETCH", "1") != "0"
+        self._pf_stream = None
+        self._pf_event = None
 
     # ------------------------------------------------------------------ loading
     def _model_path(self):
@@ -120,17 +124,54 @@ class VideoFlowCore:
             fmaps, net, inp = self.model.encode(x)
             return self.model.refine(fmaps, net, inp, select=Tn - 2, crop=(t, l, H, W), out=out)
 
-    def compute_flow_from_frames(self, frames, keys, out=None):
+    def compute_flow_from_frames(self, frames, keys, out=None, next_window=None):
         """Same result as compute_flow_from_tensor(stack(frames)[None]) for a window given frame by frame, with the
         encoders' outputs cached per frame.  frames: T tensors [3, H, W] on the device (values as the caller would stack
         them), or callables returning one (evaluated only for frames whose features are not cached, so a cached frame
-        is not even uploaded); keys: T hashable frame identities (None = do not cache that frame)."""
+        is not even uploaded); keys: T hashable frame identities (None = do not cache that frame).
+        next_window: (frames, keys) of the window the caller will ask for next: its missing encoder outputs (one new frame
+        per encoder in a sliding pass) are computed on a side stream WHILE this window iterates, and are cache hits then."""
         if self.model is None:
             raise RuntimeError("VideoFlow model not loaded. Call load_model() first.")
         Tn = len(frames)
         if Tn < 3 or len(keys) != Tn:
             raise ValueError("compute_flow_from_frames needs >= 3 frames and one key per frame")
         centre = range(1, Tn - 1)
+        with torch.no_grad():
+            ent = self._ensure_features(frames, keys)
+            if next_window is not None and self.prefetch and self.feature_cache_frames > 0:
+                self._prefetch(*next_window)
+            H, W = ent[0]["hw"]
+            l, r, tp, b = pad_amounts(H, W)
+            fmaps = torch.stack([e["fmap"] for e in ent])
+            net = torch.stack([ent[i]["ctx"][0] for i in centre])
+            inp = torch.stack([ent[i]["ctx"][1] for i in centre])
+            return self.model.refine(fmaps, net, inp, select=Tn - 2, crop=(tp, l, H, W), out=out, frame_keys=keys)
+
+    def _prefetch(self, frames, keys):
+        """_ensure_features for a future window on the prefetch stream (ordered after everything queued so far on the
+        current stream; the current stream waits for it at its next _ensure_features)."""
+        if len(frames) != len(keys) or len(frames) < 3 or any(k is None for k in keys) or not torch.cuda.is_available():
+            return
+        main = torch.cuda.current_stream(self.device)
+        if self._pf_stream is None:
+            self._pf_stream = torch.cuda.Stream(self.device)
+        ev = torch.cuda.Event()
+        ev.record(main)
+        with torch.cuda.stream(self._pf_stream):
+            self._pf_stream.wait_event(ev)
+            self._ensure_features(frames, keys, prefetch=True)
+            self._pf_event = torch.cuda.Event()
+            self._pf_event.record(self._pf_stream)
+
+    def _ensure_features(self, frames, keys, prefetch=False):
+        """Cache entries ({"fmap", "ctx", "hw"}) of the window's frames, running the encoders on what is missing."""
+        Tn = len(frames)
+        centre = range(1, Tn - 1)
+        cur = torch.cuda.current_stream(self.device) if (torch.cuda.is_available() and str(self.device).startswith("cuda")) else None
+        if not prefetch and self._pf_event is not None:
+            cur.wait_event(self._pf_event)               # features (and the encoders' static buffers) the prefetch stream is writing
+            self._pf_event = None
         ent = [self._feat.get(k) if k is not None else None for k in keys]
         need_f = [i for i in range(Tn) if ent[i] is None]
         need_c = [i for i in centre if ent[i] is None or ent[i]["ctx"] is None]
@@ -153,35 +194,37 @@ class VideoFlowCore:
             return loaded[j]
         uniq_f = sorted({first[keys[i] if keys[i] is not None else ("#", i)] for i in need_f})
         uniq_c = sorted({first[keys[i] if keys[i] is not None else ("#", i)] for i in need_c})
-        with torch.no_grad():
-            new = {}
-            same = uniq_f == uniq_c and len(uniq_f) > 0
-            xf = torch.cat([tensor(j)[0] for j in uniq_f]) if uniq_f else None
-            xc = xf if same else (torch.cat([tensor(j)[0] for j in uniq_c]) if uniq_c else None)
-            fm, ctx = self.model.encode_new_frames(xf, xc) if (uniq_f or uniq_c) else (None, None)      # the two encoders side by side
-            for n, j in enumerate(uniq_f):
-                new[j] = {"fmap": fm[n], "ctx": None, "hw": tensor(j)[1:]}
-            for n, j in enumerate(uniq_c):
-                e = new.get(j) or ent[j]
-                e["ctx"] = (ctx[0][n], ctx[1][n])
-            self.cache_stats["fnet_runs"] += len(uniq_f)
-            self.cache_stats["cnet_runs"] += len(uniq_c)
+        new = {}
+        same = uniq_f == uniq_c and len(uniq_f) > 0
+        xf = torch.cat([tensor(j)[0] for j in uniq_f]) if uniq_f else None
+        xc = xf if same else (torch.cat([tensor(j)[0] for j in uniq_c]) if uniq_c else None)
+        fm, ctx = self.model.encode_new_frames(xf, xc) if (uniq_f or uniq_c) else (None, None)      # the two encoders side by side
+        for n, j in enumerate(uniq_f):
+            new[j] = {"fmap": fm[n], "ctx": None, "hw": tensor(j)[1:]}
+        for n, j in enumerate(uniq_c):
+            e = new.get(j) or ent[j]
+            e["ctx"] = (ctx[0][n], ctx[1][n])
+        self.cache_stats["fnet_runs"] += len(uniq_f)
+        self.cache_stats["cnet_runs"] += len(uniq_c)
+        if not prefetch:
             self.cache_stats["fnet_hits"] += Tn - len(need_f)
             self.cache_stats["cnet_hits"] += len(centre) - len(need_c)
-            for i in range(Tn):
-                if ent[i] is None:
-                    ent[i] = new[first[keys[i] if keys[i] is not None else ("#", i)]]
-                if keys[i] is not None and self.feature_cache_frames > 0:
-                    self._feat[keys[i]] = ent[i]
-                    self._feat.move_to_end(keys[i])
-            while len(self._feat) > self.feature_cache_frames:
-                self._feat.popitem(last=False)
-            H, W = ent[0]["hw"]
-            l, r, tp, b = pad_amounts(H, W)
-            fmaps = torch.stack([e["fmap"] for e in ent])
-            net = torch.stack([ent[i]["ctx"][0] for i in centre])
-            inp = torch.stack([ent[i]["ctx"][1] for i in centre])
-            return self.model.refine(fmaps, net, inp, select=Tn - 2, crop=(tp, l, H, W), out=out, frame_keys=keys)
+        for i in range(Tn):
+            if ent[i] is None:
+                ent[i] = new[first[keys[i] if keys[i] is not None else ("#", i)]]
+            if keys[i] is not None and self.feature_cache_frames > 0:
+                self._feat[keys[i]] = ent[i]
+                self._feat.move_to_end(keys[i])
+        while len(self._feat) > self.feature_cache_frames:
+            self._feat.popitem(last=False)
+        if cur is not None:
+            # cached tensors are produced and consumed on two streams (prefetch / caller): the caching allocator must not hand
+            # a dropped entry's memory to the other stream while this stream's reads are still queued
+            for e in ent:
+                for t in (e["fmap"],) + (tuple(e["ctx"]) if e["ctx"] is not None else ()):
+                    if t.is_cuda:
+                        t.record_stream(cur)
+        return ent
 
     def clear_feature_cache(self):
         self._feat.clear()

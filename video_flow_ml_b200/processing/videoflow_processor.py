@@ -119,6 +119,8 @@ class VideoFlowProcessor:
         t = self._dev_frames.get(key)
         if t is not None:
             self._dev_frames.move_to_end(key)
+            if t.is_cuda:
+                t.record_stream(torch.cuda.current_stream(t.device))      # uploaded on the prefetch stream, read on this one (or vice versa)
             return t
         if f.dtype == np.uint8:
             ring = getattr(self, "_pin_ring", None)
@@ -160,6 +162,19 @@ class VideoFlowProcessor:
         keys = [self._frame_key(f) for f in seq]
         return seq, keys
 
+    def _lazy_window(self, cw, rect=None):
+        """(frames on demand, keys) for VideoFlowCore.compute_flow_from_frames; rect = (x, y, w, h) selects a tile."""
+        seq, keys = cw
+        lazy = [(lambda f=f, k=k: self._chw(self._device_frame(f, k), rect)) for f, k in zip(seq, keys)]
+        return lazy, (keys if rect is None else [k + rect for k in keys])
+
+    def _next_window(self, frames, frame_idx):
+        """The window a sliding pass asks for next (frame_idx + 1), for the core's encoder prefetch."""
+        if frame_idx + 1 >= len(frames):
+            return None
+        cw = self._cached_window(frames, frame_idx + 1)
+        return None if cw is None else self._lazy_window(cw)
+
     # ------------------------------------------------------------------ inference
     def compute_optical_flow(self, frames, frame_idx, return_device=False):
         """-> np.float32 [H, W, 2] like the reference (:164-187).  return_device=True keeps the [H, W, 2] flow on the GPU
@@ -169,9 +184,7 @@ class VideoFlowProcessor:
             raise RuntimeError("Model not loaded. Call load_model() first.")
         cw = self._cached_window(frames, frame_idx)
         if cw is not None:
-            seq, keys = cw
-            lazy = [(lambda f=f, k=k: self._chw(self._device_frame(f, k))) for f, k in zip(seq, keys)]
-            flow = self.core.compute_flow_from_frames(lazy, keys)
+            flow = self.core.compute_flow_from_frames(*self._lazy_window(cw), next_window=self._next_window(frames, frame_idx))
         else:
             flow = self.core.compute_flow_from_tensor(self.prepare_frame_sequence(frames, frame_idx))
         if return_device:
@@ -211,13 +224,14 @@ class VideoFlowProcessor:
         full = torch.zeros((2, height, width), dtype=torch.float32, device=self.device)
         cw = self._cached_window(frames, frame_idx)
         window = self.prepare_frame_sequence(frames, frame_idx) if cw is None else None
+        nxt = self._cached_window(frames, frame_idx + 1) if (cw is not None and frame_idx + 1 < len(frames)) else None
         for i, ti in enumerate(tiles_info):
             if overall_pbar is not None:
                 overall_pbar.set_description(f"Tile {i+1}/{len(tiles_info)} ({ti['width']}x{ti['height']})")
             if tile_pbar is not None:
                 tile_pbar.set_description("Running VideoFlow")
                 tile_pbar.reset()
-            self._compute_tile(cw, window, ti, full)
+            self._compute_tile(cw, window, ti, full, nxt)
             if tile_pbar is not None:
                 tile_pbar.set_description("Completed")
                 tile_pbar.update(4)
@@ -227,14 +241,15 @@ class VideoFlowProcessor:
             return full.permute(1, 2, 0)
         return full.permute(1, 2, 0).cpu().numpy()
 
-    def _compute_tile(self, cw, window, ti, full):
-        """One tile of one output frame, written by the upsampling kernel into its place in `full` [2, H, W]."""
+    def _compute_tile(self, cw, window, ti, full, nxt=None):
+        """One tile of one output frame, written by the upsampling kernel into its place in `full` [2, H, W].
+        nxt: the cached window of the next output frame (its new frame's tile is encoded beside this tile's iterations)."""
         x, y, w, h = ti['x'], ti['y'], ti['width'], ti['height']
         if cw is not None:          # per-(frame, tile) encoder cache; the frame itself is uploaded once for all its tiles
             seq, keys = cw
             rect = (x, y, w, h)
-            lazy = [(lambda f=f, k=k: self._chw(self._device_frame(f, k), rect)) for f, k in zip(seq, keys)]
-            self.core.compute_flow_from_frames(lazy, [k + rect for k in keys], out=full[:, y:y + h, x:x + w])
+            self.core.compute_flow_from_frames(*self._lazy_window(cw, rect), out=full[:, y:y + h, x:x + w],
+                                               next_window=None if nxt is None else self._lazy_window(nxt, rect))
         else:
             tile = window[..., y:y + h, x:x + w].contiguous()
             self.core.compute_flow_from_tensor(tile, out=full[:, y:y + h, x:x + w])
@@ -243,7 +258,8 @@ class VideoFlowProcessor:
         """Sharded tile mode (sharding.shard_tile_chunks): compute ONE tile of frame `frame_idx` into `full` [2, H, W]."""
         cw = self._cached_window(frames, frame_idx)
         window = self.prepare_frame_sequence(frames, frame_idx) if cw is None else None
-        self._compute_tile(cw, window, tile_info, full)
+        nxt = self._cached_window(frames, frame_idx + 1) if (cw is not None and frame_idx + 1 < len(frames)) else None
+        self._compute_tile(cw, window, tile_info, full, nxt)
 
     # ------------------------------------------------------------------ misc API
     def is_model_loaded(self):
