@@ -401,7 +401,7 @@ def test_pyramid_reuse_between_sliding_windows_is_bit_exact():
         frames = [f.copy() for f in orig]
         p = _proc("fp16", sd, iters=3)
         eng = p.core.model
-        assert eng.tiled and p.core.prefetch
+        assert eng.tiled
         p.core.prefetch = prefetch
         eng.pyramid_cache = cache
         got = [p.compute_optical_flow(frames, i) for i in order]
