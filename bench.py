@@ -317,11 +317,17 @@ class FlowJob:
         """All of this rank's output frames; host_out=True is the public-API end-to-end call (numpy out)."""
         p = self.proc
         if self.units is None:
+            trace = [] if (host_out and os.environ.get("VFML_BENCH_TRACE")) else None
             for f in self.my_frames:
                 if host_out:
+                    t0 = time.perf_counter()
                     self.last_np = p.compute_optical_flow_tiled(frames, f)
+                    if trace is not None:
+                        trace.append(round((time.perf_counter() - t0) * 1000.0, 2))
                 else:
                     self.out[self.slot[f]].copy_(p.compute_optical_flow_tiled(frames, f, return_device=True).permute(2, 0, 1))
+            if trace:
+                print("e2e per-frame ms:", trace, file=sys.stderr)
         else:
             for ti, a, b in self.units:
                 for f in range(a, b):

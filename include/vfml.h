@@ -284,8 +284,8 @@ int vfml_gemm(const vfml_gemm_desc* d, vfml_stream_t s);
 /* Optional, outside CUDA graph capture (it SYNCHRONISES the stream): times the kernels that can run this descriptor -- the
  * general tcgen05 kernel and the weight-stationary cluster kernel in its single-CTA and CTA-pair modes -- on the caller's
  * buffers, and makes later vfml_gemm calls of the same (device, M, N, K, epilogue) use the fastest.  Never changes results
- * beyond fp16 rounding of identical math.  Returns 0 / 1 / 2 (general / cluster single / cluster pair) or a negative
- * vfml_status; descriptors whose output overlaps an input are left on the general kernel.  Same reference code as vfml_gemm. */
+ * beyond fp16 rounding of identical math.  Returns 0 (general kernel) or 1 + 16 * pair + cluster_size of the chosen cluster
+ * configuration, or a negative vfml_status; descriptors whose output overlaps an input are left on the general kernel.  Same reference code as vfml_gemm. */
 int vfml_gemm_autotune(const vfml_gemm_desc* d, vfml_stream_t s);
 /* 1 if vfml_gemm would run this descriptor on the tcgen05 tensor-core kernel (fp16 operands, 16-byte
  * aligned bases and pitches), 0 if on the exact fp32 FFMA kernel. */

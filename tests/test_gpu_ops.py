@@ -261,7 +261,7 @@ def test_gemm_tensor_core(ops, M, N, K):
             close(got, want, 2e-3, 2e-3)
 
 
-@pytest.mark.parametrize("pair,cs", [(0, 1), (0, 2), (0, 4), (0, 8), (1, 2), (1, 4), (1, 8)])
+@pytest.mark.parametrize("pair,cs", [(0, 1), (0, 2), (0, 3), (0, 4), (0, 5), (0, 8), (1, 2), (1, 4), (1, 6), (1, 8)])
 @pytest.mark.parametrize("M,N,K", [(1408, 486, 324), (1300, 324, 486), (2176, 768, 512), (640, 128, 128), (1100, 600, 400), (900, 172, 600),
                                    (777, 193, 100), (512, 20, 64)])
 def test_gemm_weight_stationary_cluster_sizes(ops, monkeypatch, pair, cs, M, N, K):

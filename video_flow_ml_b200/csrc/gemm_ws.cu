@@ -190,7 +190,12 @@ gemm_ws_kernel(const __grid_constant__ WsMaps maps, const WsParams p) {
         long long t_wait = 0, t0 = tr ? clock64() : 0;
         if (!p.b_is_const && t_first < t_end && elect_one()) load_weights();
         __syncwarp();
-        const int slice_rows = WS_BM / sharers;
+        // the A block is fetched in 2^k equal shares (swizzle atoms are 8 rows) by the first 2^k sharers; with 3 or 5..7 column
+        // tiles the remaining sharers only receive
+        int loaders = 1;
+        while (loaders * 2 <= sharers) loaders *= 2;
+        const bool i_load = ct < loaders;
+        const int slice_rows = WS_BM / loaders;
         const uint32_t slice_off = (uint32_t)(ct * slice_rows) * 128u;
         for (int tile = t_first; tile < t_end; tile += t_step) {
             const int m0 = tile * TM + c * WS_BM;
@@ -208,7 +213,7 @@ gemm_ws_kernel(const __grid_constant__ WsMaps maps, const WsParams p) {
                     if (!PAIR || c == 0) mbar_expect_tx(&full_bar[s], (uint32_t)nblk * WS_A_BYTES * (PAIR ? 2u : 1u));
 #pragma unroll
                     for (int i = 0; i < WS_MAX_SK; ++i) {
-                        if (i < nblk) {
+                        if (i < nblk && i_load) {
                             uint8_t* dst = sA + (size_t)s * stage_bytes + (size_t)i * WS_A_BYTES + slice_off;
                             if (PAIR) {
                                 if (sharers > 1) tma_load_3d_2sm_multicast(&maps.A, leader_bar_addr(&full_bar[s]), dst, (kb + i) * WS_BK, m0 + ct * slice_rows, 0, mask_a);
@@ -499,7 +504,7 @@ bool gemm_ws_supported(const vfml_gemm_desc& d) {
 struct WsConfig { int pair, cs, bn, stages, sk, clusters; size_t smem; double cost; };
 
 // > 0: declined (no configuration whose weight slice fits shared memory): the caller falls back to gemm_tc
-int gemm_ws(const vfml_gemm_desc& d, cudaStream_t st, int mode) {      // mode: -1 = cost model (or VFML_WS_PAIR), 0 = single CTAs, 1 = CTA pairs
+int gemm_ws(const vfml_gemm_desc& d, cudaStream_t st, int mode, int cluster) {      // mode: -1 = cost model (or VFML_WS_PAIR), 0 = single CTAs, 1 = CTA pairs; cluster: 0 = cost model (or VFML_WS_CS)
     const int ki = ws_kernel_index(d);
     static PerDevice<bool> attr_done;
     if (!attr_done.get()) {
@@ -513,15 +518,14 @@ int gemm_ws(const vfml_gemm_desc& d, cudaStream_t st, int mode) {      // mode: 
     // experiments / tests: pin the mode and the cluster size (read per call)
     const char* e_cs = getenv("VFML_WS_CS");
     const char* e_pair = getenv("VFML_WS_PAIR");
-    const int force_cs = e_cs ? atoi(e_cs) : 0, force_pair = mode >= 0 ? mode : e_pair ? atoi(e_pair) : -1;
+    const int force_cs = cluster > 0 ? cluster : e_cs ? atoi(e_cs) : 0, force_pair = mode >= 0 ? mode : e_pair ? atoi(e_pair) : -1;
     // co-resident clusters per (kernel, mode, cluster size): GPC boundaries leave some SMs out for the larger sizes
-    static PerDevice<int[WS_NUM_KERNELS][2][4]> occ_cache;
+    static PerDevice<int[WS_NUM_KERNELS][2][WS_MAX_CS + 1]> occ_cache;
     WsConfig best{};
     best.cost = 1e30;
     for (int pair = 0; pair < 2; ++pair) {
         if (force_pair >= 0 && pair != force_pair) continue;
-        for (int ci = pair; ci < 4; ++ci) {
-            const int cs = 1 << ci;
+        for (int cs = pair ? 2 : 1; cs <= WS_MAX_CS; cs += pair ? 2 : 1) {
             if (force_cs && cs != force_cs) continue;
             const int n_ct = pair ? cs / 2 : cs;                                 // column tiles = CTAs sharing A rows
             const int bn = (cdiv(d.N, n_ct) + 15) / 16 * 16;
@@ -533,7 +537,7 @@ int gemm_ws(const vfml_gemm_desc& d, cudaStream_t st, int mode) {      // mode: 
             if (fixed + (pair ? 3 : 2) * stage_bytes > WS_SMEM_MAX) continue;
             const int stages = (int)std::min<size_t>(std::min<size_t>(WS_MAX_STAGES, (size_t)cdiv(nkb, sk) * 2), (WS_SMEM_MAX - fixed) / stage_bytes);
             const size_t smem = fixed + (size_t)stages * stage_bytes;
-            int& occ = occ_cache.get()[ki][pair][ci];
+            int& occ = occ_cache.get()[ki][pair][cs];
             if (occ == 0) {
                 cudaLaunchConfig_t q{};
                 q.gridDim = dim3(cs * 64); q.blockDim = dim3(WS_THREADS); q.dynamicSmemBytes = WS_SMEM_MAX;
@@ -544,10 +548,12 @@ int gemm_ws(const vfml_gemm_desc& d, cudaStream_t st, int mode) {      // mode: 
                 int n = 0;
                 if (cudaOccupancyMaxActiveClusters(&n, ws_kernels[ki].fn[pair], &q) != cudaSuccess || n <= 0) {
                     cudaGetLastError();
-                    n = device_sms() / cs * 3 / 4;
+                    occ = -1;                      // this cluster size cannot be scheduled on this device
+                } else {
+                    occ = std::max(1, std::min(n, device_sms() / cs));
                 }
-                occ = std::max(1, std::min(n, device_sms() / cs));
             }
+            if (occ < 0) continue;
             const int row_tiles = cdiv(d.M, pair ? 2 * WS_BM : WS_BM);
             const int clusters = std::min(occ, row_tiles);
             // cycles per CTA and tile: the slowest of the tensor pipe, the shared-memory ports (~100 B/clk) and the SM's L2 link
@@ -568,7 +574,9 @@ int gemm_ws(const vfml_gemm_desc& d, cudaStream_t st, int mode) {      // mode: 
     WsMaps maps;
     {
         const cuuint64_t dims[3] = {(cuuint64_t)d.K, (cuuint64_t)d.M, 1}, strides[2] = {(cuuint64_t)d.lda * 2, (cuuint64_t)d.lda * d.M * 2};
-        const cuuint32_t box[3] = {(cuuint32_t)WS_BK, (cuuint32_t)(WS_BM / n_ct), 1};
+        int loaders = 1;
+        while (loaders * 2 <= n_ct) loaders *= 2;
+        const cuuint32_t box[3] = {(cuuint32_t)WS_BK, (cuuint32_t)(WS_BM / loaders), 1};
         int rc = ws_map(&maps.A, d.A, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, "A");
         if (rc) return rc;
     }
@@ -666,12 +674,12 @@ int gemm_ws(const vfml_gemm_desc& d, cudaStream_t st, int mode) {      // mode: 
     return VFML_OK;
 }
 
-// ---- which kernel runs a layer: measured, not modelled.  vfml_gemm_autotune() times the general kernel (gemm_tc) and the two
-// modes of this one on the caller's descriptor and remembers the winner per (device, M, N, K, epilogue); vfml_gemm() looks it
-// up.  Layers that were never tuned run on gemm_tc, as before.
+// ---- which kernel runs a layer: measured, not modelled.  vfml_gemm_autotune() times the general kernel (gemm_tc) and every
+// feasible (mode, cluster size) of this one on the caller's descriptor and remembers the winner per (device, M, N, K,
+// epilogue); vfml_gemm() looks it up.  Layers that were never tuned run on gemm_tc, as before.
 using WsKey = std::tuple<int, int, int, int, uint32_t>;
 static std::mutex ws_mu;
-static std::map<WsKey, int> ws_choice;            // 0 = gemm_tc, 1 = gemm_ws single, 2 = gemm_ws pair
+static std::map<WsKey, int> ws_choice;            // 0 = gemm_tc, else 1 + 16 * pair + cluster size
 static WsKey ws_key(const vfml_gemm_desc& d) { return WsKey(device_index(), d.M, d.N, d.K, d.epi & ~VFML_EPI_WEIGHTS); }
 
 int gemm_ws_choice(const vfml_gemm_desc& d) {
@@ -679,6 +687,11 @@ int gemm_ws_choice(const vfml_gemm_desc& d) {
     std::lock_guard<std::mutex> lk(ws_mu);
     auto it = ws_choice.find(ws_key(d));
     return it == ws_choice.end() ? 0 : it->second;
+}
+
+int gemm_ws_run_choice(const vfml_gemm_desc& d, cudaStream_t st, int choice) {
+    if (choice < 0) return gemm_ws(d, st, -1, 0);
+    return gemm_ws(d, st, ((choice - 1) >> 4) & 1, (choice - 1) & 15);
 }
 
 int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st);
@@ -703,16 +716,18 @@ int gemm_autotune(const vfml_gemm_desc& d, cudaStream_t st) {
     VFML_CUDA(cudaEventCreate(&e1));
     float best_ms = 1e30f, tc_ms = 1e30f;
     int best = 0;
-    for (int cand = 0; cand < 3; ++cand) {
-        auto run = [&]() { return cand == 0 ? gemm_tc(d, st) : gemm_ws(d, st, cand - 1); };
+    for (int cand = 0; cand <= 32; ++cand) {       // 0: gemm_tc; 1 + 16 pair + cs
+        const int pair = cand ? ((cand - 1) >> 4) & 1 : 0, cs = cand ? (cand - 1) & 15 : 0;
+        if (cand && (cs < 1 || cs > WS_MAX_CS || (pair && (cs & 1)))) continue;
+        auto run = [&]() { return cand == 0 ? gemm_tc(d, st) : gemm_ws(d, st, pair, cs); };
         int rc = 0;
-        for (int i = 0; i < 3 && rc == 0; ++i) rc = run();
+        for (int i = 0; i < 2 && rc == 0; ++i) rc = run();
         if (rc > 0) continue;                      // this mode has no configuration for the shape
         if (rc < 0) { cudaEventDestroy(e0); cudaEventDestroy(e1); return rc; }
         float ms_min = 1e30f;
-        for (int rep = 0; rep < 3; ++rep) {        // best of three groups of six back-to-back launches
+        for (int rep = 0; rep < 3; ++rep) {        // best of three groups of five back-to-back launches
             VFML_CUDA(cudaEventRecord(e0, st));
-            for (int i = 0; i < 6; ++i) run();
+            for (int i = 0; i < 5; ++i) run();
             VFML_CUDA(cudaEventRecord(e1, st));
             VFML_CUDA(cudaEventSynchronize(e1));
             float ms = 0;
@@ -725,9 +740,11 @@ int gemm_autotune(const vfml_gemm_desc& d, cudaStream_t st) {
     if (best != 0 && best_ms > 0.97f * tc_ms) best = 0;       // switch only for a clear win
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
-    if (getenv("VFML_GEMM_AUTOTUNE_LOG"))
-        fprintf(stderr, "[gemm autotune] M=%d N=%d K=%d epi=%u: gemm_tc %.1f us, best %s %.1f us\n", d.M, d.N, d.K, d.epi, tc_ms * 1000 / 6,
-                best == 0 ? "gemm_tc" : best == 1 ? "gemm_ws single" : "gemm_ws pair", best_ms * 1000 / 6);
+    if (getenv("VFML_GEMM_AUTOTUNE_LOG")) {
+        if (best) fprintf(stderr, "[gemm autotune] M=%d N=%d K=%d epi=%u: gemm_tc %.1f us, best gemm_ws %s cluster %d: %.1f us\n", d.M, d.N, d.K, d.epi, tc_ms * 200,
+                          ((best - 1) >> 4) & 1 ? "pair" : "single", (best - 1) & 15, best_ms * 200);
+        else fprintf(stderr, "[gemm autotune] M=%d N=%d K=%d epi=%u: gemm_tc %.1f us stays\n", d.M, d.N, d.K, d.epi, tc_ms * 200);
+    }
     std::lock_guard<std::mutex> lk(ws_mu);
     ws_choice[ws_key(d)] = best;
     return best;

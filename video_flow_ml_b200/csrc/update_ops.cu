@@ -371,7 +371,7 @@ int dwconv_tiled(const void* x, void* y, int n_img, int h, int w, int C, int64_t
 int gemm_ffma(const vfml_gemm_desc& d, cudaStream_t st);
 int gemm_tc(const vfml_gemm_desc& d, cudaStream_t st);
 bool gemm_tc_supported(const vfml_gemm_desc& d);
-int gemm_ws(const vfml_gemm_desc& d, cudaStream_t st, int mode);
+int gemm_ws_run_choice(const vfml_gemm_desc& d, cudaStream_t st, int choice);
 bool gemm_ws_supported(const vfml_gemm_desc& d);
 int gemm_ws_choice(const vfml_gemm_desc& d);
 int gemm_autotune(const vfml_gemm_desc& d, cudaStream_t st);
@@ -420,9 +420,9 @@ extern "C" int vfml_gemm(const vfml_gemm_desc* d, vfml_stream_t s) {
     // fp16 operands with TMA-compatible alignment -> tcgen05 tensor-core kernel; fp32 (exact tier) and
     // oddly aligned fp16 views -> FFMA kernel.  Both are libvfml kernels with identical semantics.
     if (gemm_ws_supported(*d)) {           // the update block's big pointwise layers: the cluster kernel where it measured faster
-        const int choice = gemm_ws_choice(*d);          // 0: gemm_tc (also: never tuned), 1 / 2: gemm_ws single / pair, -1: pinned by the environment
+        const int choice = gemm_ws_choice(*d);          // 0: gemm_tc (also: never tuned), > 0: a gemm_ws mode + cluster size, -1: pinned by the environment
         if (choice != 0) {
-            rc = gemm_ws(*d, to_stream(s), choice < 0 ? -1 : choice - 1);
+            rc = gemm_ws_run_choice(*d, to_stream(s), choice);
             if (rc <= 0) return rc;        // > 0: declined (weight slice does not fit), fall through
         }
     }
