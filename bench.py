@@ -471,7 +471,7 @@ def roofline_gemm(torch, ops, eng, Fc, P, dev):
     _, tpeak, src = peaks()
     Np = Fc * P
     rb = lambda n, c: torch.randn((n, (c + 15) // 16 * 16), device=dev).to(eng.dt)[:, :c]
-    calls, flops, abytes = [], 0.0, 0.0
+    calls, lib_calls, flops, abytes = [], [], 0.0, 0.0
     for M, C, Co in ((2 * Np, 324, 128), (Np, 256, 192), (Np, 128, 64), (Np, 400, 172), (Np, 512, 128), (Np, 128, 4)):
         hid = int(1.5 * C)
         x, t1, x2, x3, o_ = rb(M, C), rb(M, hid), rb(M, C), rb(M, C), rb(M, Co)
@@ -482,12 +482,31 @@ def roofline_gemm(torch, ops, eng, Fc, P, dev):
                   lambda x=x3, w=wpw, o=x2, b=bc: ops.gemm(x, w, o, bias=b, res=x, act="gelu", weights=True),
                   lambda x=x2, w=w2a, o=t1, b=bh: ops.gemm(x, w, o, bias=b, act="gelu", weights=True),
                   lambda x=t1, w=w2b, o=o_, b=bo: ops.gemm(x, w, o, bias=b, weights=True)]
+        # the same products through the vendor library (cuBLAS via torch.matmul on contiguous fp16 operands, NO bias / residual /
+        # GELU: those would be further kernels): what a library GEMM reaches on these small-K shapes
+        for a_, w_ in ((x, w1a), (t1, w1b), (x3, wpw), (x2, w2a), (t1, w2b)):
+            ac, wc = a_.contiguous(), w_.contiguous().t()
+            oc = torch.empty((ac.shape[0], wc.shape[1]), device=dev, dtype=eng.dt)
+            lib_calls.append(lambda ac=ac, wc=wc, oc=oc: torch.matmul(ac, wc, out=oc))
         flops += 2.0 * M * (3 * hid * C + C * C + hid * Co)
         abytes += 2.0 * M * (C + hid + hid + C + C + C + C + C + hid + hid + Co + C + C)      # activations read + written + residuals, fp16
     g_ms = _graph_time(torch, calls, 4)
     ach = flops / (g_ms * 1e-3) / 1e12
-    return {"kernel": "gemm_tc_kernel", "bound": "tensor", "achieved": ach, "peak": tpeak, "unit": "TFLOP/s", "frac": ach / tpeak,
-            "traffic": None, "traffic_source": "not captured in this run (ncu --set full summaries: profiles/)", "peak_source": src,
+    lib = None
+    try:
+        l_ms = _graph_time(torch, lib_calls, 4)
+        lib = {"us_per_iteration": l_ms * 1000.0, "achieved": flops / (l_ms * 1e-3) / 1e12, "unit": "TFLOP/s",
+               "note": "cuBLAS (torch.matmul, fp16, contiguous operands) on the same 30 shapes WITHOUT the fused bias / residual / GELU / dw1 "
+                       "epilogues: the library's own ceiling for K = 128..768 layers, for comparison with `achieved`"}
+    except Exception as e:
+        lib = {"error": repr(e)}
+    return {"kernel": "gemm_tc_kernel (+ gemm_ws_kernel on the layers where vfml_gemm_autotune measured it faster)", "bound": "tensor",
+            "achieved": ach, "peak": tpeak, "unit": "TFLOP/s", "frac": ach / tpeak, "library_same_shapes": lib,
+            "traffic": 69511168 + 4625408,
+            "traffic_source": "ncu --set full capture of round 2 (profiles/r2_ncu_gemm_dwconv_summary.txt, cold caches): dram__bytes_read.sum + "
+                              "dram__bytes_write.sum of ONE launch, the layer convc1.ffn1.2 (42240 x 324 x 486, residual + GELU + dw1), whose "
+                              "algorithmic bytes are 95.8 MB (A + residual read, D written; the weights stay resident); not re-measured in this run",
+            "peak_source": src,
             "launches": len(calls), "flops_per_iteration": flops, "algorithmic_bytes_per_iteration": abytes,
             "us_per_iteration": g_ms * 1000.0,
             "note": "the 30 pointwise-convolution GEMMs of one update iteration (SURVEY 8d: 114.4 GMAC minus the depthwise and "
