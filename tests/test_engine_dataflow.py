@@ -137,3 +137,18 @@ def test_engine_dataflow_long_sequences(mof_weights, T, H, W):
     mid = (T - 2) // 2                               # the flow VideoFlowCore returns: centre frame -> next
     sel = eng.refine(of, on, oi, select=mid)
     assert (sel - want[0, mid]).abs().max() < 2e-3
+
+
+def test_pyramid_pair_keys_identify_shared_pyramids():
+    """MOFEngine._pair_keys: (centre, partner) identity of every pyramid slot; a window shifted by one frame shares all
+    but the last forward and backward pair with its predecessor, a jump or an edited frame does not."""
+    from video_flow_ml_b200.mof import MOFEngine
+    Fc = 3
+    a = MOFEngine._pair_keys(list("abcde"), Fc)
+    b = MOFEngine._pair_keys(list("bcdef"), Fc)
+    assert a == (("b", "c"), ("c", "d"), ("d", "e"), ("b", "a"), ("c", "b"), ("d", "c"))
+    shared = lambda new, prev: all(new[j] == prev[j + 1] and new[Fc + j] == prev[Fc + j + 1] for j in range(Fc - 1))
+    assert shared(b, a)
+    assert not shared(MOFEngine._pair_keys(list("cdefg"), Fc), a)            # a jump of two frames
+    assert not shared(MOFEngine._pair_keys(["b", "c", "D", "e", "f"], Fc), a)   # frame d was edited (new key)
+    assert MOFEngine._pair_keys(["a", None, "c", "d", "e"], Fc) is None and MOFEngine._pair_keys(None, Fc) is None
