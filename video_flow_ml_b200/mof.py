@@ -140,6 +140,7 @@ class MOFEngine:
         # re-use of correlation pyramids between consecutive sliding windows (refine(frame_keys=...)); VFML_PYRAMID_CACHE=0 disables
         self.pyramid_cache = os.environ.get("VFML_PYRAMID_CACHE", "1") != "0"
         self.pyramid_slides = 0          # windows that re-used their predecessor's pyramids
+        self.encode_per_frame = os.environ.get("VFML_ENCODE_PER_FRAME", "1") != "0"      # see encode_new_frames
         self.use_side_stream = os.environ.get("VFML_NO_SIDE_STREAM") is None
 
     # ------------------------------------------------------------------ buffers
@@ -344,7 +345,20 @@ class MOFEngine:
         (tanh(net), relu(inp)) [nc, 128, h, w] each; either may be None.  The two encoders run on two streams, and the
         steady-state shapes (one new frame each: ~60 small library launches per encoder) are replayed from a CUDA graph."""
         with self._guard():
-            if not (self.use_graph and self.dev.type == "cuda" and max(0 if xf is None else xf.shape[0], 0 if xc is None else xc.shape[0]) <= 1):
+            nf, nc = (0 if xf is None else xf.shape[0]), (0 if xc is None else xc.shape[0])
+            if self.use_graph and self.dev.type == "cuda" and max(nf, nc) > 1 and self.encode_per_frame:
+                # a cold window (T + T-2 frames) goes through the same one-frame graphs as the steady state, frame by frame: no
+                # large-batch library workspaces to allocate (sporadic ~0.4 s stalls of the first window of a clip were traced to
+                # that path), the same kernels -- hence bit-identical features -- whether a frame is encoded alone or in a window
+                fms, nets, inps = [], [], []
+                for i in range(max(nf, nc)):
+                    fm_i, ctx_i = self.encode_new_frames(xf[i:i + 1] if i < nf else None, xc[i:i + 1] if i < nc else None)
+                    if fm_i is not None:
+                        fms.append(fm_i)
+                    if ctx_i is not None:
+                        nets.append(ctx_i[0]); inps.append(ctx_i[1])
+                return (torch.cat(fms) if fms else None), ((torch.cat(nets), torch.cat(inps)) if nets else None)
+            if not (self.use_graph and self.dev.type == "cuda" and max(nf, nc) <= 1):
                 return self._encode_new_body(xf, xc)
             key = (None if xf is None else tuple(xf.shape), None if xc is None else tuple(xc.shape))
             graphs = self.__dict__.setdefault("_enc_graphs", {})
