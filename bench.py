@@ -544,9 +544,9 @@ def roofline_lookup(torch, ops, eng, fmaps, Fc, hp, wp, dev):
     alg = 2 * Fc * P * (4 * 100 * es + 8 + 324 * es)     # per pixel-direction 100 texels / level read + coords + 324 written
     ach = alg / (ms * 1e-3) / 1e9
     return {"kernel": kern, "bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm,
-            "traffic": 74438912 + 3937792 if eng.tiled else None,
-            "traffic_source": "ncu --set full capture of round 1 at commit 641d11c (profiles/r1_lookup_tiled_ncu_summary.txt, cold L2): "
-                              "dram__bytes_read.sum + dram__bytes_write.sum per launch; not re-measured in this run" if eng.tiled else None,
+            "traffic": 63700992 + 3190272 if eng.tiled else None,
+            "traffic_source": "ncu --set full capture of round 2 (profiles/r2_ncu_lookup_dwconv15_summary.txt, one launch from inside the bench "
+                              "command, cold L2): dram__bytes_read.sum + dram__bytes_write.sum per launch; not re-measured in this run" if eng.tiled else None,
             "peak_source": src, "algorithmic_bytes_per_launch": alg, "us_per_launch": ms * 1000.0}
 
 

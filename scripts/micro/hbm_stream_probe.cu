@@ -20,7 +20,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 
 // tiles walked like the split-K aggregate: CTA = (row tile, K split); consecutive boxes of a CTA = consecutive k blocks
-__global__ void __launch_bounds__(64, 1) probe(const __grid_constant__ CUtensorMap map, int mode, int row_tiles, int kblocks, int splits, uint32_t* sink) {
+__global__ void __launch_bounds__(64, 1) probe(const __grid_constant__ CUtensorMap map, const __grid_constant__ CUtensorMap mapB, int mode, int with_b, int row_tiles, int kblocks, int splits, uint32_t* sink) {
     extern __shared__ __align__(1024) uint8_t raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~(uintptr_t)1023);
     __shared__ uint64_t full[STAGES];
@@ -49,7 +49,10 @@ __global__ void __launch_bounds__(64, 1) probe(const __grid_constant__ CUtensorM
         if (!box_of(i, rt, kb)) return false;
         if (kb >= kblocks) kb = kblocks - 1;
         const int s = (int)(i % STAGES);
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&full[s])), "r"((uint32_t)BOX_BYTES) : "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&full[s])), "r"((uint32_t)BOX_BYTES * (with_b ? 2u : 1u)) : "memory");
+        if (with_b)      // the GEMM's other operand: the same 128 x 64 block of a small (L2-resident) matrix for every row tile
+            asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                         ::"r"(smem_u32(smem + (STAGES + s) * BOX_BYTES)), "l"(&mapB), "r"(smem_u32(&full[s])), "r"(kb * 64), "r"(0) : "memory");
         if (mode == 0)
             asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                          ::"r"(smem_u32(smem + s * BOX_BYTES)), "l"(&map), "r"(smem_u32(&full[s])), "r"(kb * 64), "r"(rt * 128) : "memory");
@@ -92,25 +95,30 @@ int main() {
     cudaMalloc(&buf, bytes);
     cudaMalloc(&sink, 4);
     cudaMemset(buf, 1, bytes);
-    cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, STAGES * BOX_BYTES + 1024);
+    cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * STAGES * BOX_BYTES + 1024);
     int sms = 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
     const CUtensorMap m_rows = make_map(buf, P, (uint64_t)NM * P, (uint64_t)P * 2, 64, 128);
     const CUtensorMap m_blk = make_map(buf, 64, (uint64_t)row_tiles * kblocks * 128, 128, 64, 128);
+    void* bufB;
+    cudaMalloc(&bufB, (size_t)128 * P * 2);
+    cudaMemset(bufB, 1, (size_t)128 * P * 2);
+    const CUtensorMap m_b = make_map(bufB, P, 128, (uint64_t)P * 2, 64, 128);
     printf("%d matrices of %d x %d fp16 = %.0f MB, %d SMs, %d x 16 KB boxes in flight per CTA\n", NM, P, P, bytes / 1e6, sms, STAGES);
-    for (int splits : {1, 2, 5})
-        for (int mode = 0; mode < 2; ++mode) {
+    for (int splits : {2, 5})
+        for (int with_b = 0; with_b < 2; ++with_b) {
+            const int mode = 0;
             cudaEvent_t e0, e1;
             cudaEventCreate(&e0); cudaEventCreate(&e1);
             const int grid = sms;
-            probe<<<grid, 64, STAGES * BOX_BYTES + 1024>>>(mode ? m_blk : m_rows, mode, row_tiles, kblocks, splits, sink);
+            probe<<<grid, 64, 2 * STAGES * BOX_BYTES + 1024>>>(mode ? m_blk : m_rows, m_b, mode, with_b, row_tiles, kblocks, splits, sink);
             cudaEventRecord(e0);
-            for (int r = 0; r < 5; ++r) probe<<<grid, 64, STAGES * BOX_BYTES + 1024>>>(mode ? m_blk : m_rows, mode, row_tiles, kblocks, splits, sink);
+            for (int r = 0; r < 5; ++r) probe<<<grid, 64, 2 * STAGES * BOX_BYTES + 1024>>>(mode ? m_blk : m_rows, m_b, mode, with_b, row_tiles, kblocks, splits, sink);
             cudaEventRecord(e1);
             cudaError_t e = cudaDeviceSynchronize();
             float ms;
             cudaEventElapsedTime(&ms, e0, e1);
-            printf("K splits %d, %-44s %7.1f us per pass  %5.2f TB/s  %s\n", splits, mode ? "contiguous 16 KB blocks" : "row-major, 128 rows x 128 B per box",
+            printf("K splits %d, %-44s %7.1f us per pass  %5.2f TB/s of A  %s\n", splits, with_b ? "A from HBM + the B block from L2 per k block" : "A only",
                    ms * 1e3 / 5, bytes / (ms / 5 * 1e-3) / 1e12, e == cudaSuccess ? "" : cudaGetErrorString(e));
         }
     return 0;
