@@ -364,7 +364,7 @@ class MOFEngine:
             graphs = self.__dict__.setdefault("_enc_graphs", {})
             g = graphs.pop(key, None)
             if g is None:
-                while len(graphs) >= 4:
+                while len(graphs) >= 12:        # 3 encoder combinations (fnet + cnet, fnet only, cnet only) x the tile shapes of a clip
                     graphs.pop(next(iter(graphs)))
                 static = [None if t is None else t.float().clone() for t in (xf, xc)]
                 self._encode_new_body(*static)              # eager warm-up (library handles, autotuning) before the capture
