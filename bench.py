@@ -750,6 +750,21 @@ def c1_extras(torch, ops, job, cfg, args, iters, dev, world):
                                        "note": "exact tier (FFMA kernels, <= 1e-2 px vs the reference on every fixture)"}}
             del j32
             torch.cuda.empty_cache()
+            # the same tier with its products on the tensor cores (opt-in: three fp16 products per fp32 product, gemm_split.cu)
+            ops.set_fp32_split(True)
+            try:
+                j32 = FlowJob(cfg, dev, "fp32", iters, 1, 0, 3)
+                f32, n32 = j32.clip(offset=330000)
+                timed_job(torch, None, j32, 1, f32, n32, host_out=False)
+                f32, n32 = j32.clip(offset=340000)
+                ms32, _ = timed_job(torch, None, j32, 1, f32, n32, host_out=False)
+                extra["tiers"]["fp32_split"] = {"value": 3000.0 / ms32, "unit": "frames/s", "steps": 3,
+                                                "note": "opt-in (VFML_FP32_SPLIT=1): fp32 products as 3 fp16 tcgen05 products, 22-bit operands; "
+                                                        "1.2e-4 px on the well-conditioned fixture, not exact on the ill-conditioned one"}
+                del j32
+                torch.cuda.empty_cache()
+            finally:
+                ops.set_fp32_split(False)
         except Exception as e:
             extra["tiers"] = {"fp32": {"error": f"{type(e).__name__}: {e}"[:200]}}
     # ---- the reference's op sequence on this GPU and on the host cores

@@ -291,6 +291,18 @@ int vfml_gemm_autotune(const vfml_gemm_desc* d, vfml_stream_t s);
  * aligned bases and pitches), 0 if on the exact fp32 FFMA kernel. */
 int vfml_gemm_uses_tensor_cores(const vfml_gemm_desc* d);
 
+/* Tensor-core path for fp32 operands (the exact tier's pointwise layers): x = hi + lo with hi = fp16(x), lo = fp16(x - hi);
+ * A B^T ~= Ahi Bhi^T + Ahi Blo^T + Alo Bhi^T as ONE fp16 tcgen05 GEMM over a tripled K with fp32 accumulation (relative error
+ * ~2^-21 per product), then the fp32 epilogue of vfml_gemm (alpha, bias, residual, erf-GELU / ReLU, dw1) in a second pass.
+ * Same reference code as vfml_gemm.  d: fp32-in descriptor, batch 1, no VFML_EPI_ADDTO; d->B is ignored in favour of
+ * b_split = the weight as written by vfml_gemm_split_weight ([N, 3 * roundup8(K)] fp16, vfml_gemm_split_weight_bytes);
+ * workspace: vfml_gemm_split_workspace(M, N, K) bytes.  |x| must stay below the fp16 range (65504). */
+size_t vfml_gemm_split_weight_bytes(int N, int K);
+int vfml_gemm_split_weight(const float* w, int N, int K, int64_t ldb, void* out, vfml_stream_t s);
+size_t vfml_gemm_split_workspace(int M, int N, int K);
+int vfml_gemm_f32_split(const vfml_gemm_desc* d, const void* b_split, void* workspace, size_t workspace_bytes,
+                        vfml_stream_t s);
+
 /* Depthwise k x k convolution over rows layout with the PCBlock residual + GELU fused:
  *   y = gelu(x + dwconv_k(x) + b)     stack.py:25-26
  * x, y: [n_img*h*w, pitch] (`dtype`), C channels from column 0; weight fp32 TAP-MAJOR [k*k, C]

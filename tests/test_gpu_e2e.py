@@ -388,6 +388,23 @@ def test_feature_cache_equals_uncached_and_saves_encoder_passes():
     assert p.core.cache_stats["fnet_runs"] == before["fnet_runs"] + 1 and p.core.cache_stats["cnet_runs"] == before["cnet_runs"] + 1
 
 
+def test_mof_fp32_split_tier_matches_reference_golden(golden):
+    """Opt-in tensor-core route of the fp32 tier (ops.set_fp32_split: fp32 products as three fp16 tensor-core products):
+    within 1e-3 px of the REFERENCE on the gain-1.0 fixture (measured 1.2e-4; the FFMA tier: 3.6e-5)."""
+    from video_flow_ml_b200 import ops
+    g = golden("mof_e2e_g10.npz")
+    sd = omof.mof_synthetic_weights(0, gain=1.0)
+    ops.set_fp32_split(True)
+    try:
+        p = _proc("fp32", sd)
+        frames = cases.mof_case()
+        for idx in (2, 5):
+            flow = p.compute_optical_flow(list(frames), idx)
+            assert epe(flow, g[f"flow_{idx}"]) <= 1e-3, (idx, epe(flow, g[f"flow_{idx}"]))
+    finally:
+        ops.set_fp32_split(False)
+
+
 def test_pyramid_reuse_between_sliding_windows_is_bit_exact():
     """A window that follows its predecessor by one frame re-uses the correlation pyramids of the shared centre frames
     (slot copies + one new pair instead of 2 (T-2) pairs, a second CUDA graph): bit-identical flows with and without

@@ -299,6 +299,44 @@ def test_gemm_weight_stationary_cluster_sizes(ops, monkeypatch, pair, cs, M, N, 
         assert float(wide[:, off + N:].float().sub(7.0).abs().max()) == 0 and float(wide[:, 8 + N:off].float().sub(7.0).abs().max()) == 0
 
 
+@pytest.mark.parametrize("M,N,K", [(1000, 172, 600), (4224, 486, 324), (7040, 128, 7040), (640, 20, 17)])
+def test_gemm_fp32_split_tensor_cores(ops, M, N, K):
+    """gemm_split.cu: fp32 product as three fp16 tensor-core products (hi / lo split, power-of-two operand scaling, fp32
+    accumulation) + the fp32 epilogue pass; against the CPU double result: 22-bit operands -> <= 2e-6 of sum |a||w| (1e-5 at K = 7040),
+    also with operands ~1e-4 (softmax rows) and ~1e3 that a plain fp16 cast would flush or overflow."""
+    r = torch.Generator().manual_seed(M + N + K)
+    for a_scale, w_scale in ((1.0, 1.0), (1e-4, 3.0), (2e3, 1e-2)):
+        a = torch.randn((M, K), generator=r) * a_scale
+        w = torch.randn((N, K), generator=r) * w_scale / K ** 0.5
+        bias, dww, dwb = torch.randn(N, generator=r), torch.randn(N, generator=r) * 0.3, torch.randn(N, generator=r) * 0.3
+        res = torch.randn((M, N), generator=r)
+        ops.set_fp32_split(True)
+        try:
+            for kw in (dict(), dict(bias=bias, act="gelu"), dict(bias=bias, res=res, act="gelu", dw=(dww, dwb)), dict(res=res, alpha=0.5),
+                       dict(bias=bias, act="relu", weights=True)):
+                want = kw.get("alpha", 1.0) * (a.double() @ w.double().t())
+                if "bias" in kw:
+                    want = want + bias.double()
+                if "res" in kw:
+                    want = want + res.double()
+                if kw.get("act") == "gelu":
+                    want = torch.nn.functional.gelu(want)
+                elif kw.get("act") == "relu":
+                    want = torch.relu(want)
+                if "dw" in kw:
+                    want = torch.nn.functional.gelu(want + (dww.double() * want + dwb.double()))
+                kwc = {k: (tuple(cu(x) for x in v) if isinstance(v, tuple) else cu(v) if torch.is_tensor(v) else v) for k, v in kw.items()}
+                got = rows_buf(M, N)
+                A = rows_buf(M, K, pad=16); A.copy_(a)
+                ops.gemm(A, cu(w), got, **kwc)
+                scale = float((a.double().abs() @ w.double().abs().t()).max()) + float(want.abs().max())
+                err = float((got.double().cpu() - want).abs().max())
+                # (the tensor core's fp32 accumulation is not round-to-nearest: over 3 x 7040 / 16 accumulation steps it shows)
+                assert err <= (2e-6 if K <= 1024 else 1e-5) * scale, (kw.keys(), a_scale, err, scale)
+        finally:
+            ops.set_fp32_split(False)
+
+
 def test_gemm_tensor_core_large_k_and_strided_views(ops):
     """attention-shaped products: K = 7040 (110 k-blocks through the stage ring), operands that are column
     slices of wider buffers."""

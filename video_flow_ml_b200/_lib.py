@@ -56,6 +56,10 @@ PROTOTYPES = {
     "vfml_taa_init": (i32, [vp, i32, vp, i32, i32, vp]),
     "vfml_gemm": (i32, [C.POINTER(GemmDesc), vp]),
     "vfml_gemm_autotune": (i32, [C.POINTER(GemmDesc), vp]),
+    "vfml_gemm_split_weight_bytes": (sz, [i32, i32]),
+    "vfml_gemm_split_weight": (i32, [vp, i32, i32, i64, vp, vp]),
+    "vfml_gemm_split_workspace": (sz, [i32, i32, i32]),
+    "vfml_gemm_f32_split": (i32, [C.POINTER(GemmDesc), vp, vp, sz, vp]),
     "vfml_gemm_uses_tensor_cores": (i32, [C.POINTER(GemmDesc)]),
     "vfml_dwconv_res_gelu": (i32, [vp, vp, i32, i32, i32, i32, i64, i64, vp, vp, i32, i32, vp]),
     "vfml_dwconv_packed_bytes": (sz, [i32, i32]),

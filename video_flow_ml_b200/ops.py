@@ -472,8 +472,49 @@ def gemm(a, w, out, bias=None, res=None, act=None, dw=None, alpha=1.0, addto=Fal
         rc = _lib.load().vfml_gemm_autotune(C.byref(d), _stream())
         if rc < 0:
             _lib.check(rc, "gemm_autotune")
+    if a.dtype == torch.float32 and out.dtype == torch.float32 and _FP32_SPLIT[0] and not addto and M >= 512 and N >= 16 and K >= 16:
+        # the exact tier's products on the tensor cores: fp32 = fp16 hi + fp16 lo, three products in one fp16 GEMM (gemm_split.cu)
+        lib = _lib.load()
+        sid = torch.cuda.current_stream().cuda_stream      # concurrent branches run on their own streams: scratch per stream
+        dev_i = a.device.index
+        nb = lib.vfml_gemm_split_weight_bytes(N, K)
+        if weights:                    # layer constants: split once, keyed by their storage (the cache keeps the tensor alive)
+            wkey = (w.data_ptr(), N, K, w.stride(0), dev_i)
+            ent = _SPLIT_WEIGHTS.get(wkey)
+            if ent is None:
+                w3 = torch.empty(nb, dtype=torch.uint8, device=w.device)
+                _lib.check(lib.vfml_gemm_split_weight(_p(w), N, K, w.stride(0), _p(w3), _stream()), "gemm_split_weight")
+                while len(_SPLIT_WEIGHTS) >= 512:
+                    _SPLIT_WEIGHTS.pop(next(iter(_SPLIT_WEIGHTS)))
+                ent = _SPLIT_WEIGHTS[wkey] = (w3, w)
+            w3 = ent[0]
+        else:                          # an activation as the second operand (q k^T, attn v): split per call
+            bkey = ("b", sid, N, K, dev_i)
+            w3 = _SPLIT_SCRATCH.get(bkey)
+            if w3 is None:
+                w3 = _SPLIT_SCRATCH[bkey] = torch.empty(nb, dtype=torch.uint8, device=w.device)
+            _lib.check(lib.vfml_gemm_split_weight(_p(w), N, K, w.stride(0), _p(w3), _stream()), "gemm_split_weight")
+        skey = ("a", sid, M, N, K, dev_i)
+        wsb = _SPLIT_SCRATCH.get(skey)
+        if wsb is None:
+            wsb = _SPLIT_SCRATCH[skey] = torch.empty(lib.vfml_gemm_split_workspace(M, N, K), dtype=torch.uint8, device=a.device)
+        _lib.check(lib.vfml_gemm_f32_split(C.byref(d), _p(w3), _p(wsb), wsb.numel(), _stream()), "gemm_f32_split")
+        return out
     _lib.check(_lib.load().vfml_gemm(C.byref(d), _stream()), "gemm")
     return out
+
+
+# Tensor-core route of fp32 products (opt-in: VFML_FP32_SPLIT=1 or ops.set_fp32_split(True)).  22-bit operands instead of 24:
+# 1.2e-4 px from the reference on the well-conditioned fixtures (FFMA: 3.6e-5) at 1.5x the speed of the FFMA tier, but 6e-2 px on
+# the ill-conditioned gain-1.4 set where the FFMA kernels hold 2e-3 -- so the default fp32 tier stays exact.
+_FP32_SPLIT = [os.environ.get("VFML_FP32_SPLIT", "0") == "1"]
+
+
+def set_fp32_split(enabled):
+    _FP32_SPLIT[0] = bool(enabled)
+
+_SPLIT_WEIGHTS = {}
+_SPLIT_SCRATCH = {}
 
 
 _GEMM_AUTOTUNE = [False]
