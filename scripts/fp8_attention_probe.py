@@ -1,6 +1,6 @@
 """CPU: would storing the GMA attention matrix in fp8 hold the parity bound?
 
-The aggregate streams one fp16 attention matrix (P x P, 99 MB at 1280 x 704) per centre frame and iteration from HBM:
+The aggregate streams one fp16 attention matrix (P x P, 99 MB at 436 x 1024) per centre frame and iteration from HBM:
 297 MB of the update step's traffic.  e4m3 with one scale per row would halve that.  This script rounds the oracle's
 attention matrix to fp16 / to row-scaled e4m3 and prints how far the returned flow moves (32 iterations, every weight
 set of tests/golden).  Bound for a reduced-precision tier: 5e-2 px.   -> profiles/r2_fp8_attention_probe.txt

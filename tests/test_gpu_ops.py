@@ -487,6 +487,42 @@ def test_tiled_volume_pair_launch(ops):
     assert torch.equal(oa, sa) and torch.equal(ob, sb)
 
 
+@pytest.mark.parametrize("n,C,h,w", [(2, 128, 55, 128), (1, 128, 47, 156), (3, 64, 20, 31), (1, 128, 8, 8), (2, 64, 9, 33),
+                                     (1, 128, 17, 135), (6, 128, 24, 40)])
+def test_corr_volume_fused_epilogue_is_bit_identical(ops, monkeypatch, n, C, h, w):
+    """North star (1): the pyramid comes out of the volume GEMM's epilogue (corr_fused.cu: levels 0 and 1 from the TMEM
+    accumulators, 2 and 3 from the tiled level 1).  Every byte of every level -- padding texels of the edge tiles included,
+    the buffers start poisoned -- equals the unfused path (GEMM -> row-major fp16 level 0 -> corr_tile_pyramid_kernel), and
+    level 0 matches the fp64 product.  Shapes: C1, C3, odd sizes with M / N tails, the 8 x 8 minimum, six pairs in one launch."""
+    r = np.random.default_rng(n * 1000 + h * w + C)
+    f1 = cu(T(r.standard_normal((n, C, h, w)).astype(np.float32)))
+    f2 = cu(T(r.standard_normal((n, C, h, w)).astype(np.float32)))
+
+    def run(fused):
+        monkeypatch.setenv("VFML_CORR_FUSED", "1" if fused else "0")
+        out = ops.TiledPyramid([torch.full_like(l, 0xAB) for l in ops._tiled_levels(n * h * w, h, w, f1.device)], n, h, w)
+        launches = ops._lib.launch_count()
+        ops.corr_volume_pyramid_tiled(f1, f2, out=out)
+        torch.cuda.synchronize()
+        return out, ops._lib.launch_count() - launches
+
+    fused, n_fused = run(True)
+    plain, n_plain = run(False)
+    assert n_fused == 4 and n_plain >= 4          # 2 x rows copies + (fused GEMM, levels 2-3) | (GEMM, pyramid)
+    for l, (a, b) in enumerate(zip(fused.levels, plain.levels)):
+        assert torch.equal(a, b), (l, int((a != b).sum()))
+    # level 0 against the fp64 product of the fp16-rounded features (texel (x, y) of tile (x // 4, y // 4), x-major in the tile)
+    a16, b16 = f1.half().double().flatten(2), f2.half().double().flatten(2)
+    want = torch.einsum("ncp,ncq->npq", a16, b16) / np.sqrt(C)
+    nty = (h + 3) // 4
+    lv0 = fused.levels[0].view(torch.float16).view(n, h * w, -1, 16)
+    ys, xs = torch.meshgrid(torch.arange(h), torch.arange(w), indexing="ij")
+    tile = ((xs // 4) * nty + ys // 4).flatten().to(f1.device)
+    elem = ((xs % 4) * 4 + ys % 4).flatten().to(f1.device)
+    got = lv0[:, :, tile, elem].double()
+    assert (got - want).abs().max().item() < 2e-2 * max(1.0, want.abs().max().item() / 16)
+
+
 # ---------------------------------------------------------------- tensor-core depthwise convolution
 @pytest.mark.parametrize("k,C,n,h,w", [(15, 324, 2, 55, 128), (15, 128, 1, 20, 31), (7, 512, 1, 47, 39), (7, 64, 3, 70, 33), (15, 12, 1, 8, 8)])
 def test_dwconv_tc_matches_fp64(ops, k, C, n, h, w):

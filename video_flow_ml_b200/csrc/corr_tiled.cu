@@ -31,6 +31,9 @@
 
 namespace vfml {
 
+bool corr_fused_supported(int C, int h, int w, int num_levels);                 // corr_fused.cu
+int corr_volume_fused(const __half* r1, const __half* r2, int n_pairs, int C, int h, int w, void* const* levels, cudaStream_t st);
+
 constexpr int TL_LEVELS = 4;
 constexpr int TL_UNITS = 3;            // pixels per round
 constexpr int TL_AROW = 160;           // smem bytes per tile row (4 tiles x 32 B + 32 B: bank spread)
@@ -315,29 +318,45 @@ struct TilePyrParams {
     int lh[TL_LEVELS], lw[TL_LEVELS], ntx[TL_LEVELS], nty[TL_LEVELS];
     int soff[TL_LEVELS];      // smem offsets (elements)
     int num_levels;
+    int first;                // 0: start from the row-major level 0 (vol0); 1: levels 0 and 1 exist (corr_fused.cu), start from the TILED level 1
     int64_t rows;
 };
 
 __global__ void __launch_bounds__(256)
 corr_tile_pyramid_kernel(const TilePyrParams p) {
     extern __shared__ __align__(16) __half tp_s[];
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, nthr = blockDim.x;
     const int P0 = p.lh[0] * p.lw[0];
     for (int64_t row = blockIdx.x; row < p.rows; row += gridDim.x) {
-        const __half* src = p.vol0 + row * P0;
-        if ((P0 & 7) == 0) {
-            const uint4* s4 = reinterpret_cast<const uint4*>(src);
-            uint4* d4 = reinterpret_cast<uint4*>(tp_s);
-            for (int i = tid; i < P0 / 8; i += 256) d4[i] = __ldg(s4 + i);
+        if (p.first) {
+            // un-tile level 1: thread = (tile, x column of the tile); the 4 texels of a column are 8 contiguous bytes
+            const int lw = p.lw[1], lh = p.lh[1], nty = p.nty[1], nt = p.ntx[1] * nty;
+            const uint2* src = reinterpret_cast<const uint2*>(p.lvl[1] + row * ((int64_t)nt * 32));
+            __half* out = tp_s + p.soff[1];
+            for (int i = tid; i < nt * 4; i += nthr) {
+                const int t = i >> 2, xr = i & 3, tx = t / nty, ty = t - tx * nty, x = tx * 4 + xr;
+                const uint2 q = __ldg(src + i);
+                const __half* hv = reinterpret_cast<const __half*>(&q);
+                if (x < lw)
+                    for (int yy = 0; yy < 4; ++yy)
+                        if (ty * 4 + yy < lh) out[(ty * 4 + yy) * lw + x] = hv[yy];
+            }
         } else {
-            for (int i = tid; i < P0; i += 256) tp_s[i] = src[i];
+            const __half* src = p.vol0 + row * P0;
+            if ((P0 & 7) == 0) {
+                const uint4* s4 = reinterpret_cast<const uint4*>(src);
+                uint4* d4 = reinterpret_cast<uint4*>(tp_s);
+                for (int i = tid; i < P0 / 8; i += nthr) d4[i] = __ldg(s4 + i);
+            } else {
+                for (int i = tid; i < P0; i += nthr) tp_s[i] = src[i];
+            }
         }
         __syncthreads();
-        for (int l = 1; l < p.num_levels; ++l) {
+        for (int l = p.first + 1; l < p.num_levels; ++l) {
             const int wi = p.lw[l - 1], wo = p.lw[l], ho = p.lh[l];
             const __half* in = tp_s + p.soff[l - 1];
             __half* out = tp_s + p.soff[l];
-            for (int i = tid; i < wo * ho; i += 256) {
+            for (int i = tid; i < wo * ho; i += nthr) {
                 const int y = i / wo, x = i - y * wo;
                 const __half* s = in + (2 * y) * wi + 2 * x;
                 const float a = ((__half2float(s[0]) + __half2float(s[1])) + __half2float(s[wi])) + __half2float(s[wi + 1]);
@@ -345,11 +364,11 @@ corr_tile_pyramid_kernel(const TilePyrParams p) {
             }
             __syncthreads();
         }
-        for (int l = 0; l < p.num_levels; ++l) {
+        for (int l = p.first ? 2 : 0; l < p.num_levels; ++l) {
             const int lw = p.lw[l], lh = p.lh[l], nty = p.nty[l], nt = p.ntx[l] * nty;
             const __half* in = tp_s + p.soff[l];
             uint4* dst = reinterpret_cast<uint4*>(p.lvl[l] + row * ((int64_t)nt * 32));
-            for (int t = tid; t < nt; t += 256) {
+            for (int t = tid; t < nt; t += nthr) {
                 const int tx = t / nty, ty = t - tx * nty;
                 __align__(16) __half v[16];
 #pragma unroll
@@ -385,12 +404,8 @@ extern "C" size_t vfml_corr_tiled_slab_bytes(int h, int w, int level) {
     return (size_t)((w + 3) / 4) * ((h + 3) / 4) * 32;
 }
 
-extern "C" int vfml_corr_tile_pyramid(const void* vol0, int64_t rows, int h, int w, void* const* levels, int num_levels,
-                                      vfml_stream_t s) {
-    VFML_REQUIRE(rows >= 0 && h > 0 && w > 0, "corr_tile_pyramid: bad shape");
-    VFML_REQUIRE(num_levels >= 1 && num_levels <= TL_LEVELS, "corr_tile_pyramid: num_levels %d not in 1..4", num_levels);
-    if (rows == 0) return VFML_OK;
-    VFML_REQUIRE(vol0 && levels, "corr_tile_pyramid: null pointer");
+// first = 0: all levels from the row-major level 0; first = 1: levels 2.. from the tiled level 1 that is already in levels[1]
+static int tile_pyramid_launch(const void* vol0, int64_t rows, int h, int w, void* const* levels, int num_levels, int first, cudaStream_t st) {
     TilePyrParams p{};
     level_dims(h, w, num_levels, p.lh, p.lw, p.ntx, p.nty);
     int off = 0;
@@ -399,10 +414,11 @@ extern "C" int vfml_corr_tile_pyramid(const void* vol0, int64_t rows, int h, int
         VFML_REQUIRE(p.lh[l] > 0 && p.lw[l] > 0, "corr_tile_pyramid: level %d is empty (h=%d, w=%d)", l, h, w);
         p.lvl[l] = reinterpret_cast<uint8_t*>(levels[l]);
         p.soff[l] = off;
-        off += (p.lh[l] * p.lw[l] + 7) & ~7;
+        if (l >= first) off += (p.lh[l] * p.lw[l] + 7) & ~7;
     }
     p.vol0 = reinterpret_cast<const __half*>(vol0);
     p.num_levels = num_levels;
+    p.first = first;
     p.rows = rows;
     const size_t smem = (size_t)off * sizeof(__half);
     VFML_REQUIRE(smem <= 200 * 1024, "corr_tile_pyramid: %d x %d does not fit shared memory", h, w);
@@ -411,10 +427,20 @@ extern "C" int vfml_corr_tile_pyramid(const void* vol0, int64_t rows, int h, int
         VFML_CUDA(cudaFuncSetAttribute(corr_tile_pyramid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr.get() = smem;
     }
-    const int blocks = (int)std::min<int64_t>(rows, device_sms() * 16);
-    corr_tile_pyramid_kernel<<<blocks, 256, smem, to_stream(s)>>>(p);
+    const int threads = first ? 128 : 256;         // the level-1 slab is a quarter of level 0: smaller CTAs, more rows in flight
+    const int blocks = (int)std::min<int64_t>(rows, (int64_t)device_sms() * 16);
+    corr_tile_pyramid_kernel<<<blocks, threads, smem, st>>>(p);
     VFML_LAUNCH_CHECK("corr_tile_pyramid");
     return VFML_OK;
+}
+
+extern "C" int vfml_corr_tile_pyramid(const void* vol0, int64_t rows, int h, int w, void* const* levels, int num_levels,
+                                      vfml_stream_t s) {
+    VFML_REQUIRE(rows >= 0 && h > 0 && w > 0, "corr_tile_pyramid: bad shape");
+    VFML_REQUIRE(num_levels >= 1 && num_levels <= TL_LEVELS, "corr_tile_pyramid: num_levels %d not in 1..4", num_levels);
+    if (rows == 0) return VFML_OK;
+    VFML_REQUIRE(vol0 && levels, "corr_tile_pyramid: null pointer");
+    return tile_pyramid_launch(vol0, rows, h, w, levels, num_levels, 0, to_stream(s));
 }
 
 extern "C" size_t vfml_corr_volume_tiled_workspace(int n_pairs, int C, int h, int w) {
@@ -442,6 +468,13 @@ extern "C" int vfml_corr_volume_pyramid_tiled(const float* fmap1, const float* f
     if (rc) return rc;
     rc = vfml_nchw_to_rows(fmap2, r2, n_pairs, C, P, C, 0, VFML_F16, s);
     if (rc) return rc;
+    if (corr_fused_supported(C, h, w, num_levels)) {
+        // levels 0 and 1 straight from the accumulators (corr_fused.cu), levels 2 and 3 from the tiled level 1
+        for (int l = 0; l < num_levels; ++l) VFML_REQUIRE(levels[l], "corr_volume_pyramid_tiled: level %d is null", l);
+        rc = corr_volume_fused(r1, r2, n_pairs, C, h, w, levels, to_stream(s));
+        if (rc) return rc;
+        return tile_pyramid_launch(nullptr, (int64_t)n_pairs * P, h, w, levels, num_levels, 1, to_stream(s));
+    }
     vfml_gemm_desc d{};
     d.A = r1; d.B = r2; d.D = vol0;
     d.lda = C; d.ldb = C; d.ldd = P;
