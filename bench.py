@@ -637,7 +637,10 @@ def main():
         if hasattr(job, "proc") and hasattr(job.proc, "core"):
             job.proc.core.cache_stats.update(fnet_runs=0, cnet_runs=0, fnet_hits=0, cnet_hits=0)
         n0 = job.launches()
+        r0 = torch.cuda.memory_reserved(dev)
         ms_k, _ = timed_job(torch, dist, job, world, frames, need, host_out=False)
+        if os.environ.get("VFML_BENCH_TRACE"):      # did the caching allocator go to the driver inside the timed region?
+            print(f"resident pass {k}: {ms_k:.2f} ms, reserved {r0 >> 20} -> {torch.cuda.memory_reserved(dev) >> 20} MiB", file=sys.stderr)
         v_ms.append(ms_k)
         v_launch.append(job.launches() - n0)
         v_stats.append(dict(job.proc.core.cache_stats) if hasattr(job.proc, "core") else None)

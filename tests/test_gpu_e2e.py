@@ -388,6 +388,33 @@ def test_feature_cache_equals_uncached_and_saves_encoder_passes():
     assert p.core.cache_stats["fnet_runs"] == before["fnet_runs"] + 1 and p.core.cache_stats["cnet_runs"] == before["cnet_runs"] + 1
 
 
+def test_feature_cache_arena_recycles_slots_without_allocating():
+    """The cached per-frame features live in a fixed arena (one allocation per shape): a cache of two windows (10 slots)
+    sliding over 24 frames re-uses evicted frames' slots -- bit-identical flows to the default 96-slot cache, which never
+    evicts here -- and once the arena exists a window takes no memory from the driver (cudaMalloc stalls the launching
+    thread on the B200 VMs)."""
+    sd = omof.mof_synthetic_weights(0, gain=1.0)
+    frames = [np.ascontiguousarray(f) for f in cases.sliding_clip(0, 24, 64, 96, seed=5)]
+    p = _proc("fp16", sd, iters=3)
+    want = [p.compute_optical_flow(frames, i) for i in range(len(frames))]
+    arena = next(iter(p.core._arenas.values()))
+    assert arena.cap == 96 and len(arena.free) == 96 - 24
+    p.core.clear_feature_cache()
+    p.core.feature_cache_frames = 10
+    reserved = []
+    for i in range(len(frames)):
+        assert np.array_equal(p.compute_optical_flow(frames, i), want[i]), i
+        reserved.append(torch.cuda.memory_reserved())
+    arena = next(iter(p.core._arenas.values()))
+    assert arena.cap == 10 and len(p.core._feat) == 10 and len(arena.free) == 0
+    assert sorted(e["slot"] for e in p.core._feat.values()) == list(range(10))
+    assert reserved[-1] == reserved[8], (reserved[8], reserved[-1])        # steady state: nothing new from cudaMalloc
+    # a cache smaller than two windows is not pooled (a slot could be recycled under the window that still reads it)
+    p.core.clear_feature_cache()
+    p.core.feature_cache_frames = 4
+    assert np.array_equal(p.compute_optical_flow(frames, 12), want[12]) and not p.core._arenas
+
+
 def test_mof_fp32_split_tier_matches_reference_golden(golden):
     """Opt-in tensor-core route of the fp32 tier (ops.set_fp32_split: fp32 products as three fp16 tensor-core products):
     within 1e-3 px of the REFERENCE on the gain-1.0 fixture (measured 1.2e-4; the FFMA tier: 3.6e-5)."""

@@ -27,6 +27,33 @@ class _Config(dict):
         self[k] = v
 
 
+class _FeatureArena:
+    """Storage of the per-frame feature cache for ONE feature-map shape: `cap` slots of (fmap, net, inp), each of the three
+    allocated once.  A growing cache would otherwise take ~14 MB per new frame from the caching allocator, i.e. from
+    cudaMalloc until the cache is full (the first 96 frames of a clip): measured on the B200 VMs, those calls stall the
+    launching thread for 70 - 600 ms every few windows (profiles/r2_bench_host_stalls.txt).  Slots of evicted frames are
+    reused in place; writes and reads of a slot are ordered by the stream they are issued on."""
+
+    def __init__(self, cap):
+        self.cap = cap
+        self.free = list(range(cap - 1, -1, -1))
+        self.fmap = self.net = self.inp = None
+
+    def put_fmap(self, slot, fm):
+        if self.fmap is None:
+            self.fmap = torch.empty((self.cap,) + tuple(fm.shape), dtype=fm.dtype, device=fm.device)
+        self.fmap[slot].copy_(fm)
+        return self.fmap[slot]
+
+    def put_ctx(self, slot, net, inp):
+        if self.net is None:
+            self.net = torch.empty((self.cap,) + tuple(net.shape), dtype=net.dtype, device=net.device)
+            self.inp = torch.empty((self.cap,) + tuple(inp.shape), dtype=inp.dtype, device=inp.device)
+        self.net[slot].copy_(net)
+        self.inp[slot].copy_(inp)
+        return self.net[slot], self.inp[slot]
+
+
 class VideoFlowCore:
     def __init__(self, device, fast_mode=False, dataset='sintel', architecture='mof', variant='standard',
                  precision=None):
@@ -44,6 +71,10 @@ class VideoFlowCore:
         # windows share T-1 of their T frames, so a steady-state window encodes ONE new frame instead of T + (T-2)
         self.feature_cache_frames = int(os.environ.get("VFML_FEATURE_CACHE", "96"))
         self._feat = collections.OrderedDict()        # key -> {"fmap": [256,h,w], "ctx": (net, inp) or None}
+        # CUDA: the cached tensors live in per-shape arenas (no allocation per new frame); an arena holds at most
+        # feature_cache_frames slots and VFML_FEATURE_CACHE_MB (default 4096) megabytes, never fewer than two windows
+        self.feature_cache_bytes = int(os.environ.get("VFML_FEATURE_CACHE_MB", "4096")) << 20
+        self._arenas = {}
         self.cache_stats = {"fnet_runs": 0, "cnet_runs": 0, "fnet_hits": 0, "cnet_hits": 0}
         # encoder outputs of the NEXT window computed on a side stream while the current one iterates.  Opt-in (VFML_PREFETCH=1 or
         # core.prefetch = True): measured at C1 it hides 0.2 ms of the 1.0 ms encoder pass in the device-resident loop but makes the
@@ -90,7 +121,7 @@ class VideoFlowCore:
         self.cfg = self._make_cfg(model_path)
         if self.architecture == 'bof' and iters == 32:
             iters = 12            # VideoFlow/configs/things.py:31 (BOFNet.decoder_depth)
-        self._feat.clear()
+        self.clear_feature_cache()
         self.model = MOFEngine(state_dict, self.device, _PRECISIONS[self.precision], iters=iters,
                                encoder_dtype=_PRECISIONS[self.precision] if self.precision == "fp16" else None,
                                arch=self.architecture)
@@ -201,11 +232,18 @@ class VideoFlowCore:
         xf = torch.cat([tensor(j)[0] for j in uniq_f]) if uniq_f else None
         xc = xf if same else (torch.cat([tensor(j)[0] for j in uniq_c]) if uniq_c else None)
         fm, ctx = self.model.encode_new_frames(xf, xc) if (uniq_f or uniq_c) else (None, None)      # the two encoders side by side
+        pooled = cur is not None and self.feature_cache_frames > 0
+        keep = [e for e in ent if e is not None]
         for n, j in enumerate(uniq_f):
-            new[j] = {"fmap": fm[n], "ctx": None, "hw": tensor(j)[1:]}
+            new[j] = e = {"fmap": fm[n], "ctx": None, "hw": tensor(j)[1:]}
+            got = self._arena_slot(fm[n], Tn, keep) if (pooled and keys[j] is not None) else None
+            if got is not None:
+                e["arena"], e["slot"] = got
+                e["fmap"] = got[0].put_fmap(got[1], fm[n])
+            keep.append(e)
         for n, j in enumerate(uniq_c):
             e = new.get(j) or ent[j]
-            e["ctx"] = (ctx[0][n], ctx[1][n])
+            e["ctx"] = e["arena"].put_ctx(e["slot"], ctx[0][n], ctx[1][n]) if "arena" in e else (ctx[0][n], ctx[1][n])
         self.cache_stats["fnet_runs"] += len(uniq_f)
         self.cache_stats["cnet_runs"] += len(uniq_c)
         if not prefetch:
@@ -218,7 +256,9 @@ class VideoFlowCore:
                 self._feat[keys[i]] = ent[i]
                 self._feat.move_to_end(keys[i])
         while len(self._feat) > self.feature_cache_frames:
-            self._feat.popitem(last=False)
+            _, old = self._feat.popitem(last=False)
+            if "arena" in old:
+                old["arena"].free.append(old["slot"])
         if cur is not None:
             # cached tensors are produced and consumed on two streams (prefetch / caller): the caching allocator must not hand
             # a dropped entry's memory to the other stream while this stream's reads are still queued
@@ -230,6 +270,29 @@ class VideoFlowCore:
 
     def clear_feature_cache(self):
         self._feat.clear()
+        self._arenas.clear()
+
+    def _arena_slot(self, fm, Tn, keep):
+        """(arena, slot) for a new cached frame whose feature map is `fm`; None when the cache is too small to pool (< 2 windows).
+        A full arena takes the slot of its least recently used frame (never one of `keep`, the current window's entries)."""
+        if self.feature_cache_frames < 2 * Tn:
+            return None
+        akey = (tuple(fm.shape), fm.dtype, fm.device)
+        arena = self._arenas.get(akey)
+        if arena is None:
+            entry_bytes = 2 * fm.numel() * fm.element_size()          # fmap + (net, inp): 256 + 128 + 128 channels
+            cap = max(2 * Tn, min(self.feature_cache_frames, self.feature_cache_bytes // max(entry_bytes, 1)))
+            arena = self._arenas[akey] = _FeatureArena(cap)
+        if not arena.free:
+            for k in list(self._feat):
+                e = self._feat[k]
+                if e.get("arena") is arena and not any(e is x for x in keep):
+                    del self._feat[k]
+                    arena.free.append(e["slot"])
+                    break
+        if not arena.free:
+            return None
+        return arena, arena.free.pop()
 
     def is_model_loaded(self):
         return self.model is not None
