@@ -127,7 +127,11 @@ int vfml_alt_corr_forward(const void* fmap1, const void* fmap2, const float* coo
  * vfml_corr_tile_pyramid  : vol0 [rows, h*w] fp16 (row-major level 0) -> the tiled levels
  *                           (levels 1.. are 2x2 averages of the previous fp16 level).
  * vfml_corr_volume_pyramid_tiled : fmaps [n_pairs, C, h, w] fp32 -> tiled levels, C % 8 == 0,
- *                           workspace of vfml_corr_volume_tiled_workspace() bytes.
+ *                           workspace of vfml_corr_volume_tiled_workspace() bytes.  With 4 levels and
+ *                           C = 64 or 128 the pyramid is written by the volume GEMM's epilogue
+ *                           (corr.py:68-74 fused into :59-66: no row-major volume is materialised;
+ *                           environment VFML_CORR_FUSED=0 selects the GEMM + vfml_corr_tile_pyramid
+ *                           sequence, same bytes out).
  * vfml_corr_lookup_tiled  : radius 4, 4 levels, one or two sets (levels_b may be NULL) in one
  *                           launch; out_* are fp16 rows buffers [n_frames*h*w, out_pitch],
  *                           out_pitch % 8 == 0, out_col % 8 == 0, 16-byte aligned.  Channel
