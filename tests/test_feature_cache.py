@@ -73,3 +73,30 @@ def test_frame_keys_notice_identity_and_content():
     a[:] = 7
     assert k(a) != ka                                 # same array, rewritten in place
     assert k(a[:8]) != k(a)
+
+
+def test_feature_arena_slots_capacity_and_eviction():
+    """Arena bookkeeping of the feature cache (CUDA path of _ensure_features; exercised here with CPU tensors): capacity from the
+    frame and byte limits, never below two windows; a full arena hands out the slot of its least recently used frame that is not
+    part of the current window; caches smaller than two windows are not pooled."""
+    core = VideoFlowCore("cuda")
+    fm = torch.zeros(256, 4, 6)
+    core.feature_cache_frames = 12
+    core.feature_cache_bytes = 7 * 2 * fm.numel() * 4            # room for 7 entries: below two windows of T = 5 -> 10 slots
+    keep = []
+    for k in range(10):
+        arena, slot = core._arena_slot(fm, 5, keep)
+        assert slot == k and arena.cap == 10
+        core._feat[k] = {"fmap": arena.put_fmap(slot, fm + k), "ctx": None, "arena": arena, "slot": slot}
+    assert not arena.free and arena.fmap.shape == (10, 256, 4, 6) and arena.net is None
+    cur = [core._feat[0], core._feat[1]]                          # the current window holds the two oldest frames
+    a2, slot = core._arena_slot(fm, 5, cur)
+    assert a2 is arena and slot == 2 and list(core._feat) == [0, 1, 3, 4, 5, 6, 7, 8, 9]
+    net, inp = arena.put_ctx(slot, torch.ones(128, 4, 6), 2 * torch.ones(128, 4, 6))
+    assert arena.net.shape == (10, 128, 4, 6) and float(net.sum()) == 128 * 24 and float(inp[0, 0, 0]) == 2.0
+    assert float(core._feat[3]["fmap"][0, 0, 0]) == 3.0          # other slots untouched
+    assert core._arena_slot(torch.zeros(256, 8, 8), 5, [])[0] is not arena        # another shape, another arena
+    core.feature_cache_frames = 9                                 # < 2 windows: not pooled
+    assert core._arena_slot(fm, 5, []) is None
+    core.clear_feature_cache()
+    assert not core._arenas and not core._feat
