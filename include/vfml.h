@@ -349,11 +349,15 @@ int vfml_softmax_rows(const float* in, void* out, int64_t rows, int n, int64_t l
  *   x400[:, 304:352] = sample(mhs of frame t-1, bcoords)  (zero state before the first frame)
  *   f128 = convf1_(flow4)  (1x1 conv, 4 -> 128)            written to f128 rows
  *   mf[:, 124:128] = flow4
- * mhs lives in x400[:, 352:400]. */
+ * mhs lives in x400[:, 352:400].
+ * rot (0 <= rot < n_frames): the frames are stored in RING order -- slot f of every buffer holds the window's frame
+ * (f - rot) mod n_frames -- so "frame t+1" of slot f is slot (f + 1) mod n_frames, and the window's last / first frame
+ * (zero state) sits in slot (rot - 1) mod n_frames / rot.  The engine keeps a sliding window's per-frame state (pyramids,
+ * attention) in place and only rotates; rot = 0 is the reference's order. */
 int vfml_motion_glue(const float* fcoords, const float* bcoords, void* x400, int64_t pitch400,
                      void* f128, int64_t pitch128, void* mf, int64_t pitch_mf, int mf_col,
                      const float* convf1_w, const float* convf1_b, int n_frames, int h, int w,
-                     int dtype, vfml_stream_t s);
+                     int rot, int dtype, vfml_stream_t s);
 
 /* Fused softmax attention of the Twins-SVT stages, fp16, head dimension 32 (LocallyGroupedAttn twins_ft.py:233-261,
  * GlobalSubSampleAttn :291-312): o[b, i, h, :] = softmax_j(scale * q[b, i, h, :] . k[b, j, h, :]) v[b, j, h, :].

@@ -8,8 +8,9 @@ from video_flow_ml_b200 import ops
 
 torch.manual_seed(0)
 dev = torch.device("cuda:0")
-for name, n, C, h, w in (("C1 steady state (2 new pairs)", 2, 128, 55, 128), ("C1 cold window (6 pairs)", 6, 128, 55, 128),
-                         ("C3 (T=9: 2 new pairs)", 2, 128, 47, 156), ("4K tile 1280x1280 (2 pairs)", 2, 128, 160, 160)):
+for name, n, C, h, w in (("C1 steady state (2 x 1 new pair)", 1, 256, 55, 128), ("C1 cold window (2 x 3 pairs)", 3, 256, 55, 128),
+                         ("C3 (T=9: 2 x 1 new pair)", 1, 256, 47, 156), ("4K tile 1280x1280 (2 x 1 pair)", 1, 256, 160, 160),
+                         ("C = 128, 2 pairs at C1 size", 2, 128, 55, 128)):
     f1 = torch.randn(n, C, h, w, device=dev)
     f2 = torch.randn(n, C, h, w, device=dev)
     out = ops.TiledPyramid(ops._tiled_levels(n * h * w, h, w, dev), n, h, w)

@@ -63,8 +63,29 @@ def corr_lookup_perm(device=None):
     return real(device)
 
 
+class TiledPyramid:
+    """Stand-in for ops.TiledPyramid: levels[l] is [n*h*w, 1, h_l, w_l] (row = source pixel), so slots of source frames are
+    row ranges like in the real layout."""
+
+    def __init__(self, levels, n, h, w):
+        self.levels, self.n, self.h, self.w = levels, n, h, w
+
+
+def tiled_pyramid_alloc(n, h, w, device):
+    return TiledPyramid([torch.full((n * h * w, 1, h >> l, w >> l), float("nan")) for l in range(4)], n, h, w)
+
+
+def tiled_volume_workspace(n, Cc, h, w, device):
+    return None
+
+
 def corr_volume_pyramid_tiled(f1, f2, workspace=None, out=None):
-    return corr_volume_pyramid(f1, f2, 4)
+    levels = corr_volume_pyramid(f1, f2, 4)
+    if out is None:
+        return TiledPyramid(levels, f1.shape[0], f1.shape[2], f1.shape[3])
+    for dst, src in zip(out.levels, levels):
+        dst.copy_(src)
+    return out
 
 
 def corr_lookup_tiled(pyr_a, pyr_b, coords_a, coords_b, out_a, out_b, math_f32=False):
@@ -74,7 +95,7 @@ def corr_lookup_tiled(pyr_a, pyr_b, coords_a, coords_b, out_a, out_b, math_f32=F
         if pyr is None:
             continue
         tmp = torch.empty(out.shape, dtype=torch.float32)
-        corr_lookup(pyr, c, 4, out=tmp)
+        corr_lookup(pyr.levels, c, 4, out=tmp)
         out.copy_(tmp[:, perm].to(out.dtype))
     return out_a, out_b
 
@@ -157,14 +178,16 @@ def _sample(img, cx, cy):
     return F.grid_sample(img, grid, align_corners=True)
 
 
-def motion_glue(fc, bc, x400, f128, mf, w1, b1, n_frames, h, w):
+def motion_glue(fc, bc, x400, f128, mf, w1, b1, n_frames, h, w, rot=0):
     ys, xs = torch.meshgrid(torch.arange(h), torch.arange(w), indexing="ij")
     g = torch.stack([xs, ys], 0).float()[None]
     flow4 = torch.cat([fc - g, bc - g], 1)                                     # [F,4,h,w]
     mhs = x400[:, 352:400].float().reshape(n_frames, h, w, 48).permute(0, 3, 1, 2)
-    z = torch.zeros(1, 48, h, w)
-    nxt = torch.cat([mhs[1:], z], 0)
-    prv = torch.cat([z, mhs[:-1]], 0)
+    z = torch.zeros(48, h, w)
+    # ring order: slot f holds the window's frame (f - rot) mod F; its neighbours in window order are the adjacent slots
+    logical = [(f - rot) % n_frames for f in range(n_frames)]
+    nxt = torch.stack([mhs[(f + 1) % n_frames] if logical[f] + 1 < n_frames else z for f in range(n_frames)])
+    prv = torch.stack([mhs[(f - 1) % n_frames] if logical[f] > 0 else z for f in range(n_frames)])
     fw = _sample(nxt, fc[:, 0], fc[:, 1])
     bw = _sample(prv, bc[:, 0], bc[:, 1])
     rows = lambda t: t.permute(0, 2, 3, 1).reshape(n_frames * h * w, -1)

@@ -152,3 +152,33 @@ def test_pyramid_pair_keys_identify_shared_pyramids():
     assert not shared(MOFEngine._pair_keys(list("cdefg"), Fc), a)            # a jump of two frames
     assert not shared(MOFEngine._pair_keys(["b", "c", "D", "e", "f"], Fc), a)   # frame d was edited (new key)
     assert MOFEngine._pair_keys(["a", None, "c", "d", "e"], Fc) is None and MOFEngine._pair_keys(None, Fc) is None
+
+
+@pytest.mark.parametrize("ring", [True, False])
+def test_engine_sliding_windows_keep_per_frame_state_in_ring_order(mof_weights, ring):
+    """Consecutive windows given with frame identities (refine(frame_keys=...)): the engine keeps the pyramids -- and, in ring
+    mode, the attention matrices -- of the centre frames two windows share, computes only the new frame's, and in ring mode
+    rotates the slot order instead of moving data (motion_glue's temporal neighbours, the context rows and the selected output
+    follow the rotation).  Every window must equal a fresh engine's self-contained result; seven slides cover every rotation
+    of Fc = 3 twice; a jump and a repeated window fall back to the full build."""
+    torch.manual_seed(0)
+    frames = cases.mof_case(seed=5, n_frames=12)
+    eng = MOFEngine(mof_weights, "cpu", torch.float32, iters=2, ops=fake_ops, tiled=True)
+    eng.pyramid_ring = ring
+    order = [2, 3, 4, 5, 6, 7, 8, 9, 4, 5, 5, 6]
+    rots = []
+    for n, i in enumerate(order):
+        win = omof.pad_frames(omof.frames_to_window(frames, i, 5)).contiguous()
+        of, on, oi = omof.mof_encode(win, mof_weights)
+        keys = [("f", k) for k in range(i - 2, i + 3)]
+        fresh = MOFEngine(mof_weights, "cpu", torch.float32, iters=2, ops=fake_ops, tiled=True).refine(of, on, oi)
+        if n % 2:                                                 # all flows, in window order whatever the rotation
+            got = eng.refine(of, on, oi, frame_keys=keys)
+            assert (got - fresh).abs().max() < 1e-4, (i, (got - fresh).abs().max())
+        else:                                                     # one flow: forward of the middle centre frame / backward of the last
+            sel = 1 if n % 4 == 0 else 5
+            got = eng.refine(of, on, oi, select=sel, frame_keys=keys)
+            assert (got - fresh[0, sel]).abs().max() < 1e-4, (i, sel, (got - fresh[0, sel]).abs().max())
+        rots.append(next(iter(eng._ws.values()))["rot"])
+    assert eng.pyramid_slides == 9
+    assert rots == ([0, 1, 2, 0, 1, 2, 0, 1, 0, 1, 0, 1] if ring else [0] * 12), rots

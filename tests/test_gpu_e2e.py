@@ -434,20 +434,22 @@ def test_mof_fp32_split_tier_matches_reference_golden(golden):
 
 def test_pyramid_reuse_between_sliding_windows_is_bit_exact():
     """A window that follows its predecessor by one frame re-uses the correlation pyramids of the shared centre frames
-    (slot copies + one new pair instead of 2 (T-2) pairs, a second CUDA graph): bit-identical flows with and without
+    and their attention matrices, in place (ring order: one new pair instead of 2 (T-2) pairs, one CUDA graph per rotation):
+    bit-identical flows with and without
     (same call sequence, so the per-frame encoder cache behaves identically in both runs), also across jumps in the clip
     (re-use must not trigger) and after an in-place edit of a shared frame (its pairs are rebuilt)."""
     sd = omof.mof_synthetic_weights(0, gain=1.0)
     orig = [f.astype(np.float32) for f in cases.mof_case(seed=77, n_frames=11)]
     order = [2, 3, 4, 5, 8, 9, 3, 4]                 # slides, a jump, a slide, a jump back, a slide
 
-    def run(cache, prefetch=True):
+    def run(cache, prefetch=True, ring=True):
         frames = [f.copy() for f in orig]
         p = _proc("fp16", sd, iters=3)
         eng = p.core.model
         assert eng.tiled
         p.core.prefetch = prefetch
         eng.pyramid_cache = cache
+        eng.pyramid_ring = ring
         got = [p.compute_optical_flow(frames, i) for i in order]
         slides = [eng.pyramid_slides]                               # windows 3, 4, 5 | 9 | 4
         frames[6][:] = frames[6][:, ::-1].copy()                    # frame 6 is in two pairs the window at 5 would have re-used
@@ -466,6 +468,26 @@ def test_pyramid_reuse_between_sliding_windows_is_bit_exact():
     plain, _ = run(False, prefetch=False)
     for k, (a, b) in enumerate(zip(plain, got)):
         assert np.array_equal(a, b), ("prefetch", k, float(np.abs(a - b).max()))
+    # ring order off: pyramids moved between slots by device copies, attention recomputed every window
+    moved, slides = run(True, ring=False)
+    assert slides == [5, 5, 6]
+    for k, (a, b) in enumerate(zip(moved, got)):
+        assert np.array_equal(a, b), ("ring", k, float(np.abs(a - b).max()))
+
+
+def test_ring_order_long_windows_every_rotation():
+    """T = 7 (five centre frames): eleven consecutive windows take the ring through every rotation twice; each flow equals the
+    one a fresh pass computes for that window alone (same per-frame features through the cache: bit-identical)."""
+    sd = omof.mof_synthetic_weights(0, gain=1.0)
+    frames = [f.astype(np.float32) for f in cases.mof_case(seed=78, n_frames=18)]
+    p = _proc("fp16", sd, T=7, iters=2)
+    got = [p.compute_optical_flow(frames, i) for i in range(3, 15)]
+    assert p.core.model.pyramid_slides == 11
+    ws = next(iter(p.core.model._ws.values()))
+    assert ws["rot"] == 11 % 5 and len(ws["graphs"]) == 6          # one cold graph + one per rotation
+    p.core.model.pyramid_cache = False
+    for i, g_ in zip(range(3, 15), got):
+        assert np.array_equal(p.compute_optical_flow(frames, i), g_), i
 
 
 def test_device_resident_post_pass_matches_reference_golden(golden):

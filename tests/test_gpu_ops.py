@@ -213,9 +213,20 @@ def test_misc_update_ops(ops):
     bcd = bcc + 3 * torch.randn((Fc, 2, h, w), generator=r)
     X, F1, MF = rows_buf(Np, 400), rows_buf(Np, 128), rows_buf(Np, 128)
     X.copy_(x400)
+    x0_400 = x400.clone()
     fake_ops.motion_glue(fcd, bcd, x400, f128, mf, w1, b1, Fc, h, w)
     ops.motion_glue(cu(fcd), cu(bcd), X, F1, MF, cu(w1), cu(b1), Fc, h, w)
     close(X, x400, 2e-5); close(F1, f128, 2e-5); close(MF[:, 124:], mf[:, 124:], 1e-6)
+    # ring order (the engine keeps a sliding window's frames in place and rotates): frames rolled by `rot` slots give the
+    # rolled result, on the test double (vs rot = 0) and on the kernel (vs the test double)
+    for rot in range(1, Fc):
+        roll_r = lambda t: torch.roll(t.reshape(Fc, h * w, -1), rot, 0).reshape(Np, -1)
+        xr, fr, mr = roll_r(x0_400), torch.zeros((Np, 128)), torch.zeros((Np, 128))
+        X.copy_(xr)
+        fake_ops.motion_glue(torch.roll(fcd, rot, 0), torch.roll(bcd, rot, 0), xr, fr, mr, w1, b1, Fc, h, w, rot=rot)
+        close(xr, roll_r(x400), 1e-6); close(fr, roll_r(f128), 1e-6)
+        ops.motion_glue(cu(torch.roll(fcd, rot, 0)), cu(torch.roll(bcd, rot, 0)), X, F1, MF, cu(w1), cu(b1), Fc, h, w, rot=rot)
+        close(X, xr, 2e-5); close(F1, fr, 2e-5); close(MF[:, 124:], mr[:, 124:], 1e-6)
     # rows fill, im2col
     v = torch.randn(48, generator=r)
     ops.rows_fill(X[:, 352:400], cu(v))
@@ -487,13 +498,14 @@ def test_tiled_volume_pair_launch(ops):
     assert torch.equal(oa, sa) and torch.equal(ob, sb)
 
 
-@pytest.mark.parametrize("n,C,h,w", [(2, 128, 55, 128), (1, 128, 47, 156), (3, 64, 20, 31), (1, 128, 8, 8), (2, 64, 9, 33),
-                                     (1, 128, 17, 135), (6, 128, 24, 40)])
+@pytest.mark.parametrize("n,C,h,w", [(2, 256, 55, 128), (1, 256, 47, 156), (3, 64, 20, 31), (1, 128, 8, 8), (2, 192, 9, 33),
+                                     (1, 256, 17, 135), (6, 128, 24, 40), (1, 256, 8, 8)])
 def test_corr_volume_fused_epilogue_is_bit_identical(ops, monkeypatch, n, C, h, w):
     """North star (1): the pyramid comes out of the volume GEMM's epilogue (corr_fused.cu: levels 0 and 1 from the TMEM
     accumulators, 2 and 3 from the tiled level 1).  Every byte of every level -- padding texels of the edge tiles included,
     the buffers start poisoned -- equals the unfused path (GEMM -> row-major fp16 level 0 -> corr_tile_pyramid_kernel), and
-    level 0 matches the fp64 product.  Shapes: C1, C3, odd sizes with M / N tails, the 8 x 8 minimum, six pairs in one launch."""
+    level 0 matches the fp64 product.  Shapes: C1, C3 (C = 256: the engine's feature maps), odd sizes with M / N tails, the
+    8 x 8 minimum, six pairs in one launch, every supported channel count (64, 128, 192, 256)."""
     r = np.random.default_rng(n * 1000 + h * w + C)
     f1 = cu(T(r.standard_normal((n, C, h, w)).astype(np.float32)))
     f2 = cu(T(r.standard_normal((n, C, h, w)).astype(np.float32)))

@@ -70,7 +70,7 @@ PROTOTYPES = {
     "vfml_attention_hd32": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i64, i64, i64, i64, i64, i64, f32, vp]),
     "vfml_peg3x3": (i32, [vp, vp, i32, i32, i32, i32, i64, i64, vp, vp, i32, vp]),
     "vfml_softmax_rows": (i32, [vp, vp, i64, i32, i64, i64, i32, vp]),
-    "vfml_motion_glue": (i32, [vp, vp, vp, i64, vp, i64, vp, i64, i32, vp, vp, i32, i32, i32, i32, vp]),
+    "vfml_motion_glue": (i32, [vp, vp, vp, i64, vp, i64, vp, i64, i32, vp, vp, i32, i32, i32, i32, i32, vp]),
     "vfml_coords_add": (i32, [vp, vp, vp, i64, i32, i32, vp]),
     "vfml_coords_grid": (i32, [vp, i32, i32, i32, vp]),
     "vfml_rows_fill": (i32, [vp, i64, i32, i32, i64, vp, i32, vp]),

@@ -16,11 +16,11 @@
 //     unfused path (tests/test_gpu_ops.py::test_corr_volume_fused_epilogue_is_bit_identical).
 //   * Levels 2 and 3 (6 % of the bytes) need 16 x 16 / 32 x 32 target blocks: corr_tile_pool_kernel (corr_tiled.cu) makes them
 //     from the tiled level 1 in a small second pass.
-//   * The A tile (128 source pixels, all of K = C) stays resident in shared memory; a CTA walks a chunk of the N tiles with a
-//     2-3 stage B ring and two TMEM accumulators (the MMAs of tile i + 1 run under the stores of tile i).
+//   * The A tile (128 source pixels, all of K = C <= 256) stays resident in shared memory; a CTA walks a chunk of the N tiles with
+//     a ring of 5-6 k-block slots (32 KB each) for B and two TMEM accumulators (the MMAs of tile i + 1 run under the stores of tile i).
 //
 // Bound: the epilogue's stores -- 128 lanes x 5 tiles x 32 B per block, one sector per store instruction and lane
-// (profiles/r2_store_probe_scaling.txt: 16 B/clk/SM for this pattern), not the tensor pipe (K is only 128).
+// (profiles/r2_store_probe_scaling.txt: 16 B/clk/SM for this pattern), not the tensor pipe (K <= 256).
 #include "tcgen05.cuh"
 
 namespace vfml {
@@ -31,7 +31,7 @@ constexpr int CF_THREADS = (2 + CF_EPI_WARPS) * 32;
 constexpr int CF_A_BYTES = CF_BM * 128;          // one k-block of the resident source-pixel tile
 constexpr int CF_B_BYTES = CF_BN * 128;          // one k-block of a target tile
 constexpr int CF_BLK_BYTES = 64 * 128;           // one 8 x 8 target block of one k-block
-constexpr int CF_MAX_STAGES = 3;
+constexpr int CF_MAX_STAGES = 6;          // ring slots of ONE k-block (32 KB) of a target tile
 
 struct CfMaps {
     CUtensorMap A, B;
@@ -127,8 +127,7 @@ corr_fused_kernel(const __grid_constant__ CfMaps maps, const CfParams p) {
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(cf_smem_raw) + 1023) & ~(uintptr_t)1023);
     const int nkb = p.nkb, stages = p.stages;
     uint8_t* sA = smem;                                          // [nkb] resident source-pixel tile
-    uint8_t* sB = sA + (size_t)nkb * CF_A_BYTES;                 // [stages][nkb] target tiles
-    const uint32_t stage_bytes = (uint32_t)nkb * CF_B_BYTES;
+    uint8_t* sB = sA + (size_t)nkb * CF_A_BYTES;                 // [stages] k-blocks of target tiles
     __shared__ uint64_t full_bar[CF_MAX_STAGES], empty_bar[CF_MAX_STAGES], acc_full[2], acc_empty[2], a_full;
     __shared__ uint32_t tmem_base_s;
 
@@ -170,18 +169,18 @@ corr_fused_kernel(const __grid_constant__ CfMaps maps, const CfParams p) {
         int s = 0;
         uint32_t ph = 0;
         for (int t = t_begin; t < t_end; ++t) {
-            mbar_spin(&empty_bar[s], ph ^ 1u);
-            if (elect_one()) {
-                mbar_expect_tx(&full_bar[s], stage_bytes);
-                for (int g = 0; g < 4; ++g) {
-                    const int b = t * 4 + g, bxg = b / p.nby, by = b - bxg * p.nby;      // blocks past the last one lie right of the image: zeros
-                    for (int kb = 0; kb < nkb; ++kb)
-                        tma_load_4d(&maps.B, &full_bar[s], sB + (size_t)s * stage_bytes + (size_t)kb * CF_B_BYTES + (size_t)g * CF_BLK_BYTES,
-                                    kb * CF_BK, bxg * 8, by * 8, pair);
+            for (int kb = 0; kb < nkb; ++kb) {
+                mbar_spin(&empty_bar[s], ph ^ 1u);
+                if (elect_one()) {
+                    mbar_expect_tx(&full_bar[s], (uint32_t)CF_B_BYTES);
+                    for (int g = 0; g < 4; ++g) {
+                        const int b = t * 4 + g, bxg = b / p.nby, by = b - bxg * p.nby;      // blocks past the last one lie right of the image: zeros
+                        tma_load_4d(&maps.B, &full_bar[s], sB + (size_t)s * CF_B_BYTES + (size_t)g * CF_BLK_BYTES, kb * CF_BK, bxg * 8, by * 8, pair);
+                    }
                 }
+                __syncwarp();
+                if (++s == stages) { s = 0; ph ^= 1u; }
             }
-            __syncwarp();
-            if (++s == stages) { s = 0; ph ^= 1u; }
         }
     } else if (warp == 1) {
         // ---- MMA issuer: K / 16 instructions of 128 x 256 x 16 per tile
@@ -192,22 +191,20 @@ corr_fused_kernel(const __grid_constant__ CfMaps maps, const CfParams p) {
         uint32_t ph = 0, buf = 0, aph = 0;
         for (int t = t_begin; t < t_end; ++t) {
             mbar_spin(&acc_empty[buf], aph ^ 1u);
-            mbar_spin(&full_bar[s], ph);
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            if (elect_one()) {
-                const uint32_t tmem_d = tmem_base + buf * (uint32_t)CF_BN;
-                const uint64_t bdesc = bdesc0 + (uint64_t)((s * stage_bytes) >> 4);
-                for (int kb = 0; kb < nkb; ++kb) {
+            const uint32_t tmem_d = tmem_base + buf * (uint32_t)CF_BN;
+            for (int kb = 0; kb < nkb; ++kb) {
+                mbar_spin(&full_bar[s], ph);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                if (elect_one()) {
+                    const uint64_t ad = adesc0 + (uint64_t)((kb * CF_A_BYTES) >> 4), bd = bdesc0 + (uint64_t)((s * CF_B_BYTES) >> 4);
 #pragma unroll
-                    for (int k = 0; k < CF_BK / 16; ++k)
-                        umma_f16(tmem_d, adesc0 + (uint64_t)((kb * CF_A_BYTES) >> 4) + (uint64_t)(k * 2),
-                                 bdesc + (uint64_t)((kb * CF_B_BYTES) >> 4) + (uint64_t)(k * 2), idesc, (kb | k) ? 1u : 0u);
+                    for (int k = 0; k < CF_BK / 16; ++k) umma_f16(tmem_d, ad + (uint64_t)(k * 2), bd + (uint64_t)(k * 2), idesc, (kb | k) ? 1u : 0u);
+                    umma_commit(&empty_bar[s]);                       // the slot is free once these MMAs have read it
+                    if (kb == nkb - 1) umma_commit(&acc_full[buf]);
                 }
-                umma_commit(&empty_bar[s]);
-                umma_commit(&acc_full[buf]);
+                __syncwarp();
+                if (++s == stages) { s = 0; ph ^= 1u; }
             }
-            __syncwarp();
-            if (++s == stages) { s = 0; ph ^= 1u; }
             if (++buf == 2u) { buf = 0; aph ^= 1u; }
         }
     } else {
@@ -271,7 +268,7 @@ static int cf_map(CUtensorMap* map, const void* base, int rank, const cuuint64_t
 bool corr_fused_supported(int C, int h, int w, int num_levels) {
     const char* e = getenv("VFML_CORR_FUSED");
     if (e && e[0] == '0') return false;
-    return num_levels == 4 && (C == 64 || C == 128) && h >= 8 && w >= 8;
+    return num_levels == 4 && C >= 64 && C <= 256 && (C % 64) == 0 && h >= 8 && w >= 8;
 }
 
 // r1, r2: fp16 rows [n_pairs * P, C] of the two feature maps; writes levels[0] and levels[1] (tiled layout of corr_tiled.cu)
@@ -297,7 +294,7 @@ int corr_volume_fused(const __half* r1, const __half* r2, int n_pairs, int C, in
     p.lvl1 = static_cast<uint8_t*>(levels[1]);
     p.P = P;
     p.nkb = C / CF_BK;
-    p.stages = C == 64 ? 3 : 2;
+    p.stages = (int)std::min<size_t>(CF_MAX_STAGES, (226 * 1024 - (size_t)p.nkb * CF_A_BYTES) / CF_B_BYTES);
     p.nby = (h + 7) / 8;
     p.n_blocks = p.nby * ((w + 7) / 8);
     p.n_tiles = (p.n_blocks + 3) / 4;
@@ -319,10 +316,10 @@ int corr_volume_fused(const __half* r1, const __half* r2, int n_pairs, int C, in
     }
     const int64_t grid = units * p.chunks;
     VFML_REQUIRE(grid < (1ll << 31), "corr_volume_fused: too many tiles");
-    const size_t smem = (size_t)p.nkb * CF_A_BYTES + (size_t)p.stages * p.nkb * CF_B_BYTES + 1024;
+    const size_t smem = (size_t)p.nkb * CF_A_BYTES + (size_t)p.stages * CF_B_BYTES + 1024;
     static PerDevice<bool> attr_done;
     if (!attr_done.get()) {
-        VFML_CUDA(cudaFuncSetAttribute(corr_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+        VFML_CUDA(cudaFuncSetAttribute(corr_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_done.get() = true;
     }
     corr_fused_kernel<<<(unsigned)grid, CF_THREADS, smem, st>>>(maps, p);

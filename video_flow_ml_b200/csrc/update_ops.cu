@@ -119,6 +119,7 @@ struct GlueParams {
     void* mf; int64_t pmf; int mf_col;
     const float* w1; const float* b1;   // convf1_: [128, 4], [128]
     int F, h, w;
+    int rot;          // slot f holds the window's frame (f - rot) mod F (ring order, see vfml.h)
 };
 
 template <typename T>
@@ -165,8 +166,12 @@ __global__ void __launch_bounds__(256) motion_glue_kernel(const GlueParams p) {
         const float bcx = __ldg(p.bc + ((int64_t)f * 2) * P + pix), bcy = __ldg(p.bc + ((int64_t)f * 2 + 1) * P + pix);
         const float fl[4] = {fcx - (float)x, fcy - (float)y, bcx - (float)x, bcy - (float)y};
         T* xrow = x400 + row * p.p400;
-        warp_state<T>(x400, p.p400, f + 1, p.F, p.h, p.w, fcx, fcy, xrow + 256, lane);
-        warp_state<T>(x400, p.p400, f - 1, p.F, p.h, p.w, bcx, bcy, xrow + 304, lane);
+        // temporal neighbours in window order; the window's first / last frame has none on that side (zero state)
+        const int j = f >= p.rot ? f - p.rot : f - p.rot + p.F;
+        const int f_next = j + 1 < p.F ? (f + 1 == p.F ? 0 : f + 1) : -1;
+        const int f_prev = j > 0 ? (f == 0 ? p.F - 1 : f - 1) : -1;
+        warp_state<T>(x400, p.p400, f_next, p.F, p.h, p.w, fcx, fcy, xrow + 256, lane);
+        warp_state<T>(x400, p.p400, f_prev, p.F, p.h, p.w, bcx, bcy, xrow + 304, lane);
         T* frow = reinterpret_cast<T*>(p.f128) + row * p.p128;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
@@ -532,13 +537,14 @@ extern "C" int vfml_peg3x3(const void* x, void* y, int n_img, int h, int w, int 
 
 extern "C" int vfml_motion_glue(const float* fcoords, const float* bcoords, void* x400, int64_t pitch400, void* f128,
                                 int64_t pitch128, void* mf, int64_t pitch_mf, int mf_col, const float* convf1_w,
-                                const float* convf1_b, int n_frames, int h, int w, int dtype, vfml_stream_t s) {
+                                const float* convf1_b, int n_frames, int h, int w, int rot, int dtype, vfml_stream_t s) {
     VFML_REQUIRE(n_frames >= 0 && h > 0 && w > 0, "motion_glue: bad shape");
+    VFML_REQUIRE(rot >= 0 && (rot < n_frames || rot == 0), "motion_glue: rot=%d not in [0, n_frames)", rot);
     VFML_REQUIRE(pitch400 >= 400 && pitch128 >= 128 && mf_col >= 0 && pitch_mf >= mf_col + 128, "motion_glue: bad pitch");
     VFML_REQUIRE(valid_dtype(dtype), "motion_glue: bad dtype");
     if (n_frames == 0) return VFML_OK;
     VFML_REQUIRE(fcoords && bcoords && x400 && f128 && mf && convf1_w && convf1_b, "motion_glue: null pointer");
-    GlueParams p{fcoords, bcoords, x400, pitch400, f128, pitch128, mf, pitch_mf, mf_col, convf1_w, convf1_b, n_frames, h, w};
+    GlueParams p{fcoords, bcoords, x400, pitch400, f128, pitch128, mf, pitch_mf, mf_col, convf1_w, convf1_b, n_frames, h, w, rot};
     const int64_t total = (int64_t)n_frames * h * w;
     const int blocks = (int)std::min<int64_t>(cdiv(total, 8), device_sms() * 16);
     DISPATCH_T(dtype, (motion_glue_kernel<float><<<blocks, 256, 0, to_stream(s)>>>(p)),

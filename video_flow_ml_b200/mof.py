@@ -140,6 +140,10 @@ class MOFEngine:
         # re-use of correlation pyramids between consecutive sliding windows (refine(frame_keys=...)); VFML_PYRAMID_CACHE=0 disables
         self.pyramid_cache = os.environ.get("VFML_PYRAMID_CACHE", "1") != "0"
         self.pyramid_slides = 0          # windows that re-used their predecessor's pyramids
+        # ring order: a sliding window leaves the per-frame state of the shared centre frames (pyramids, attention matrices) in
+        # the slots it is in and only the new frame's slot is computed; slot f holds the window's centre frame (f - rot) mod Fc.
+        # VFML_PYRAMID_RING=0: the pyramids are moved down one slot instead (device copies) and the attention is recomputed.
+        self.pyramid_ring = os.environ.get("VFML_PYRAMID_RING", "1") != "0"
         self.encode_per_frame = os.environ.get("VFML_ENCODE_PER_FRAME", "1") != "0"      # see encode_new_frames
         self.use_side_stream = os.environ.get("VFML_NO_SIDE_STREAM") is None
 
@@ -181,7 +185,7 @@ class MOFEngine:
                 "logits": torch.empty((h * w, h * w), dtype=torch.float32, device=self.dev),
                 "mask": self._rows_buf(Np, 576, torch.float32),
             }
-            if self.tiled and self.dev.type == "cuda":
+            if self.tiled and (self.dev.type == "cuda" or hasattr(self.ops, "tiled_pyramid_alloc")):
                 # pyramids and the volume workspace live here, so the eager warm-up and the captured graph use the same
                 # memory (not one copy in the caching allocator and another in the graph's private pool)
                 ws["fpyr"] = self.ops.tiled_pyramid_alloc(Fc, h, w, self.dev)
@@ -381,7 +385,7 @@ class MOFEngine:
             fm, ctx = g["out"]       # static outputs: the cache keeps copies
             return (None if fm is None else fm.clone()), (None if ctx is None else (ctx[0].clone(), ctx[1].clone()))
 
-    def build_pyramids(self, fmaps, ws=None, slide=False):
+    def build_pyramids(self, fmaps, ws=None, slide=False, rot=0):
         """Forward (frames 1..T-2 vs 2..T-1) and backward (vs 0..T-3) pyramids, network.py:157-158.
         slide=True (tiled pyramids kept in the workspace): the previous window was this one shifted by one frame, so its
         pyramids of centre frames 1.. ARE this window's pyramids of centre frames 0.. (a correlation pyramid depends on its
@@ -392,11 +396,15 @@ class MOFEngine:
             Fc = T - 2
             fp, bp = ws["fpyr"], ws["bpyr"]
             P = fp.h * fp.w
-            for pyr in (fp, bp):
-                for lv in pyr.levels:
-                    for j in range(Fc - 1):          # ascending: slot j is free once it has been copied to j - 1
-                        lv[j * P:(j + 1) * P].copy_(lv[(j + 1) * P:(j + 2) * P])
-            last = lambda pyr: self.ops.TiledPyramid([lv[(Fc - 1) * P:Fc * P] for lv in pyr.levels], 1, pyr.h, pyr.w)
+            if self.pyramid_ring:
+                sn = (Fc - 1 + rot) % Fc             # the slot of the frame that left the window
+            else:
+                sn = Fc - 1
+                for pyr in (fp, bp):
+                    for lv in pyr.levels:
+                        for j in range(Fc - 1):      # ascending: slot j is free once it has been copied to j - 1
+                            lv[j * P:(j + 1) * P].copy_(lv[(j + 1) * P:(j + 2) * P])
+            last = lambda pyr: self.ops.TiledPyramid([lv[sn * P:(sn + 1) * P] for lv in pyr.levels], 1, pyr.h, pyr.w)
             c1 = fmaps[T - 2:T - 1].contiguous()
             self.ops.corr_volume_pyramid_tiled(c1, fmaps[T - 1:T].contiguous(), ws.get("vol_ws"), out=last(fp))
             self.ops.corr_volume_pyramid_tiled(c1, fmaps[T - 3:T - 2].contiguous(), ws.get("vol_ws"), out=last(bp))
@@ -411,18 +419,20 @@ class MOFEngine:
         bw = self.ops.corr_volume_pyramid(c, fmaps[0:T - 2].contiguous(), CORR_LEVELS, vdt)
         return fw, bw
 
-    def attention(self, ws, Fc, P):
-        """Attention.forward (gma.py:54-76): softmax(q k^T / sqrt(128)) per centre frame."""
+    def attention(self, ws, Fc, P, slots=None):
+        """Attention.forward (gma.py:54-76): softmax(q k^T / sqrt(128)) per centre frame (of the given slots: a sliding window
+        keeps the matrices of the frames it shares with its predecessor).  One GEMM shape per frame whatever the number of
+        slots, so a matrix does not depend on which window computed it."""
         o = self.ops
         inp = ws["x512"][:, 128:256]
-        o.gemm(inp, self.w_qk, ws["qk"])
-        for f in range(Fc):
+        for f in (range(Fc) if slots is None else slots):
+            o.gemm(inp[f * P:(f + 1) * P], self.w_qk, ws["qk"][f * P:(f + 1) * P])
             q = ws["qk"][f * P:(f + 1) * P, 0:128]
             k = ws["qk"][f * P:(f + 1) * P, 128:256]
             o.gemm(q, k, ws["logits"], alpha=128 ** -0.5)
             o.softmax_rows(ws["logits"], ws["attn"][f][:, :P])
 
-    def update_step(self, ws, fpyr, bpyr, fc, bc, Fc, h, w):
+    def update_step(self, ws, fpyr, bpyr, fc, bc, Fc, h, w, rot=0):
         """One iteration of network.py:180-197 (lookups + SKUpdateBlock6..AllDecoder2, stack.py:127-140)."""
         o = self.ops
         P = h * w
@@ -434,7 +444,7 @@ class MOFEngine:
         # the flow branch (glue + convf2, stack.py:81-87,94-95) is independent of the correlation branch: it runs on a side
         # stream and fills the partial last waves of the big convc1 / convc2 kernels
         self._fork_side()
-        o.motion_glue(fc, bc, x400, ws["f128"], mf, self.convf1_w, self.convf1_b, Fc, h, w)
+        o.motion_glue(fc, bc, x400, ws["f128"], mf, self.convf1_w, self.convf1_b, Fc, h, w, rot=rot)
         self._pcblock(ws["f128"], self.convf2, ws, Fc, h, w, [(full, full, xin[:, 192:256], None)], scratch=("hid2", "sa2", "sb2"))
         self._back_to_main()
         if self.tiled:
@@ -495,21 +505,28 @@ class MOFEngine:
         d = direction if self.arch == "mof" else 1 - direction
         return slice(576 * d, 576 * (d + 1))
 
-    def _iterations_body(self, ws, fmaps, net, inp, Fc, h, w, iters=None, slide=False):
-        """pyramids, attention, `iters` update steps.  Leaves net in x512[:, 0:128]; returns the coords."""
+    def _iterations_body(self, ws, fmaps, net, inp, Fc, h, w, iters=None, slide=False, rot=0):
+        """pyramids, attention, `iters` update steps.  Leaves net in x512[:, 0:128]; returns the coords.  Every per-frame buffer
+        is in ring order: slot f = the window's centre frame (f - rot) mod Fc (rot = 0 unless the window slid, pyramid_ring)."""
         o = self.ops
         P = h * w
-        fpyr, bpyr = self.build_pyramids(fmaps, ws, slide=slide)
+        fpyr, bpyr = self.build_pyramids(fmaps, ws, slide=slide, rot=rot)
         x512 = ws["x512"]
-        o.nchw_to_rows(net, x512[:, 0:128])
-        o.nchw_to_rows(inp, x512[:, 128:256])
+        if rot:
+            k = Fc - rot                  # centre frames k.. live in slots 0 .. rot-1, frames 0 .. k-1 in slots rot ..
+            for src, cols in ((net, slice(0, 128)), (inp, slice(128, 256))):
+                o.nchw_to_rows(src[k:], x512[:rot * P, cols])
+                o.nchw_to_rows(src[:k], x512[rot * P:, cols])
+        else:
+            o.nchw_to_rows(net, x512[:, 0:128])
+            o.nchw_to_rows(inp, x512[:, 128:256])
         if self.arch == "mof":
             o.rows_fill(ws["x400"][:, 352:400], self.init_mhs)      # init_hidden_state, stack.py:72-73
-        self.attention(ws, Fc, P)
+        self.attention(ws, Fc, P, [(Fc - 1 + rot) % Fc] if (slide and self.pyramid_ring) else None)
         fc = o.coords_grid(Fc, h, w, self.dev)
         bc = o.coords_grid(Fc, h, w, self.dev)
         for _ in range(self.iters if iters is None else iters):
-            self.update_step(ws, fpyr, bpyr, fc, bc, Fc, h, w)
+            self.update_step(ws, fpyr, bpyr, fc, bc, Fc, h, w, rot=rot)
         return fc, bc
 
     @staticmethod
@@ -531,13 +548,14 @@ class MOFEngine:
         slide = (pairs is not None and prev is not None
                  and all(pairs[j] == prev[j + 1] and pairs[Fc + j] == prev[Fc + j + 1] for j in range(Fc - 1)))
         ws["pyr_keys"] = None                      # (stays None if anything below raises: the slots are then in an unknown state)
+        rot = (ws.get("rot", 0) + 1) % Fc if (slide and self.pyramid_ring) else 0
         if not (self.use_graph and fmaps.is_cuda):
-            out = self._iterations_body(ws, fmaps, net, inp, Fc, h, w, slide=slide)
-            ws["pyr_keys"] = pairs
+            out = self._iterations_body(ws, fmaps, net, inp, Fc, h, w, slide=slide, rot=rot)
+            ws["pyr_keys"], ws["rot"] = pairs, rot
             self.pyramid_slides += int(slide)
-            return out
+            return out, rot
         graphs = ws.setdefault("graphs", {})
-        g = graphs.get(slide)
+        g = graphs.get((slide, rot))
         if g is None or g["iters"] != self.iters:
             static = [torch.empty_like(t) for t in (fmaps, net, inp)]
             for s_, t in zip(static, (fmaps, net, inp)):
@@ -550,16 +568,16 @@ class MOFEngine:
             graph = torch.cuda.CUDAGraph()
             n0 = _lib.launch_count()
             with torch.cuda.graph(graph):
-                coords = self._iterations_body(ws, *static, Fc, h, w, slide=slide)
-            g = graphs[slide] = {"graph": graph, "static": static, "coords": coords, "iters": self.iters,
-                                 "launches": _lib.launch_count() - n0}
+                coords = self._iterations_body(ws, *static, Fc, h, w, slide=slide, rot=rot)
+            g = graphs[(slide, rot)] = {"graph": graph, "static": static, "coords": coords, "iters": self.iters,
+                                        "launches": _lib.launch_count() - n0}
         for s_, t in zip(g["static"], (fmaps, net, inp)):
             s_.copy_(t)
         g["graph"].replay()
-        ws["pyr_keys"] = pairs
+        ws["pyr_keys"], ws["rot"] = pairs, rot
         self.pyramid_slides += int(slide)
         self.graph_launches += g["launches"]
-        return g["coords"]
+        return g["coords"], rot
 
     # ------------------------------------------------------------------ forward
     @torch.no_grad()
@@ -575,15 +593,21 @@ class MOFEngine:
         T, _, h, w = fmaps.shape
         Fc, P = T - 2, h * w
         ws = self._workspace(Fc, h, w)
-        fc, bc = self._run_iterations(ws, fmaps, net, inp, Fc, h, w, frame_keys)
+        (fc, bc), rot = self._run_iterations(ws, fmaps, net, inp, Fc, h, w, frame_keys)
         if select is None:
             flows = torch.empty((1, 2 * Fc, 2, 8 * h, 8 * w), dtype=torch.float32, device=self.dev)
-            mk = self.mask_rows(ws, slice(0, Fc), h, w, self._mask_chan(0))
-            o.convex_upsample8(fc, mk, out=flows[0, :Fc], flow_is_coords=True)
-            mk = self.mask_rows(ws, slice(0, Fc), h, w, self._mask_chan(1))
-            o.convex_upsample8(bc, mk, out=flows[0, Fc:], flow_is_coords=True)
+            for d, coords in enumerate((fc, bc)):
+                if rot == 0:
+                    mk = self.mask_rows(ws, slice(0, Fc), h, w, self._mask_chan(d))
+                    o.convex_upsample8(coords, mk, out=flows[0, d * Fc:(d + 1) * Fc], flow_is_coords=True)
+                    continue
+                for j in range(Fc):                   # ring order: the window's centre frame j is in slot (j + rot) mod Fc
+                    sl = (j + rot) % Fc
+                    mk = self.mask_rows(ws, slice(sl, sl + 1), h, w, self._mask_chan(d))
+                    o.convex_upsample8(coords[sl:sl + 1].contiguous(), mk, out=flows[0, d * Fc + j:d * Fc + j + 1], flow_is_coords=True)
             return flows
         direction, frame = divmod(select, Fc)
+        frame = (frame + rot) % Fc                    # its slot
         coords = (fc, bc)[direction][frame:frame + 1]
         mk = self.mask_rows(ws, slice(frame, frame + 1), h, w, self._mask_chan(direction))
         if out is None:

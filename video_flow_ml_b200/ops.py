@@ -669,7 +669,8 @@ def softmax_rows(src, dst):
     return dst
 
 
-def motion_glue(fcoords, bcoords, x400, f128, mf, w1, b1, n_frames, h, w):
+def motion_glue(fcoords, bcoords, x400, f128, mf, w1, b1, n_frames, h, w, rot=0):
+    """rot: ring position of the frames (slot f holds the window's frame (f - rot) mod n_frames), include/vfml.h."""
     _cuda(fcoords, bcoords, x400, f128, mf, w1, b1)
     _rows(x400, "x400"); _rows(f128, "f128"); _rows(mf, "mf")
     rows = n_frames * h * w
@@ -679,7 +680,7 @@ def motion_glue(fcoords, bcoords, x400, f128, mf, w1, b1, n_frames, h, w):
         raise ValueError("motion_glue: dtype mismatch")
     _lib.check(_lib.load().vfml_motion_glue(_p(_f32c(fcoords, "fc")), _p(_f32c(bcoords, "bc")), _p(x400), x400.stride(0),
                                             _p(f128), f128.stride(0), _p(mf), mf.stride(0), 0, _p(_f32c(w1, "w1")),
-                                            _p(_f32c(b1, "b1")), n_frames, h, w, _dt(x400), _stream()), "motion_glue")
+                                            _p(_f32c(b1, "b1")), n_frames, h, w, int(rot), _dt(x400), _stream()), "motion_glue")
 
 
 def coords_add(fcoords, bcoords, delta):
