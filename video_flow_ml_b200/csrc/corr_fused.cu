@@ -319,7 +319,7 @@ int corr_volume_fused(const __half* r1, const __half* r2, int n_pairs, int C, in
     const size_t smem = (size_t)p.nkb * CF_A_BYTES + (size_t)p.stages * CF_B_BYTES + 1024;
     static PerDevice<bool> attr_done;
     if (!attr_done.get()) {
-        VFML_CUDA(cudaFuncSetAttribute(corr_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        VFML_CUDA(cudaFuncSetAttribute(corr_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
         attr_done.get() = true;
     }
     corr_fused_kernel<<<(unsigned)grid, CF_THREADS, smem, st>>>(maps, p);
