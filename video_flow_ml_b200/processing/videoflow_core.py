@@ -76,10 +76,11 @@ class VideoFlowCore:
         self.feature_cache_bytes = int(os.environ.get("VFML_FEATURE_CACHE_MB", "4096")) << 20
         self._arenas = {}
         self.cache_stats = {"fnet_runs": 0, "cnet_runs": 0, "fnet_hits": 0, "cnet_hits": 0}
-        # encoder outputs of the NEXT window computed on a side stream while the current one iterates.  Opt-in (VFML_PREFETCH=1 or
-        # core.prefetch = True): measured at C1 it hides 0.2 ms of the 1.0 ms encoder pass in the device-resident loop but makes the
-        # host-frame end-to-end path erratic (36.3 -> 25 .. 36 frames/s: more distinct encoder batch shapes than its graph cache holds)
-        self.prefetch = os.environ.get("VFML_PREFETCH", "0") == "1"
+        # encoder outputs of the NEXT window computed on a side stream while the current one iterates (VFML_PREFETCH=0 or
+        # core.prefetch = False turns it off): at C1 it hides 0.2 ms of the 1.0 ms encoder pass in the device-resident loop and
+        # 0.4 ms per call from host frames (profiles/r2_ring_fused_ab.txt).  It was opt-in while the feature cache still allocated
+        # per frame: the cudaMalloc stalls of that version hit the prefetching runs hardest and were mistaken for its cost.
+        self.prefetch = os.environ.get("VFML_PREFETCH", "1") == "1"
         self._pf_stream = None
         self._pf_event = None
 
