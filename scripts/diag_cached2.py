@@ -29,7 +29,7 @@ fmaps = torch.cat([fm] * 5); net = torch.cat([ctx[0]] * 3); inp = torch.cat([ctx
 out = torch.empty((2, 436, 1024), device="cuda")
 print("refine (graph replay + mask + upsample):", ev(lambda: eng.refine(fmaps, net, inp, select=3, crop=(2, 0, 436, 1024), out=out)), "ms")
 ws = eng._workspace(3, 55, 128)
-g = ws["graphs"][False]["graph"]
+g = ws["graphs"][(False, 0)]["graph"]
 print("iteration graph replay alone:", ev(lambda: g.replay()), "ms")
 win = p.prepare_frame_sequence(fr, 12)
 print("uncached compute_flow_from_tensor:", ev(lambda: p.core.compute_flow_from_tensor(win, out=out)), "ms")
