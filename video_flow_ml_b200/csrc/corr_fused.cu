@@ -14,7 +14,7 @@
 //     thread (= one source pixel) turns 64 accumulator columns into five finished 32-byte tiles: scale, round to fp16 (the stored
 //     level 0), pool the ROUNDED values in fp32 in the order of corr_tile_pyramid_kernel, round again.  Bit-identical to the
 //     unfused path (tests/test_gpu_ops.py::test_corr_volume_fused_epilogue_is_bit_identical).
-//   * Levels 2 and 3 (6 % of the bytes) need 16 x 16 / 32 x 32 target blocks: corr_tile_pool_kernel (corr_tiled.cu) makes them
+//   * Levels 2 and 3 (6 % of the bytes) need 16 x 16 / 32 x 32 target blocks: corr_tile_pyramid_kernel (corr_tiled.cu, first = 1) makes them
 //     from the tiled level 1 in a small second pass.
 //   * The A tile (128 source pixels, all of K = C <= 256) stays resident in shared memory; a CTA walks a chunk of the N tiles with
 //     a ring of 5-6 k-block slots (32 KB each) for B and two TMEM accumulators (the MMAs of tile i + 1 run under the stores of tile i).
