@@ -144,6 +144,9 @@ class MOFEngine:
         # the slots it is in and only the new frame's slot is computed; slot f holds the window's centre frame (f - rot) mod Fc.
         # VFML_PYRAMID_RING=0: the pyramids are moved down one slot instead (device copies) and the attention is recomputed.
         self.pyramid_ring = os.environ.get("VFML_PYRAMID_RING", "1") != "0"
+        # build the pyramids on a side stream beside the attention: measured, no difference at C1 (206.2 +- 0.2 ms per 8 windows
+        # either way: the prefetched encoders already fill that phase), so off
+        self.pyramid_side_stream = os.environ.get("VFML_PYRAMID_SIDE", "0") == "1"
         self.encode_per_frame = os.environ.get("VFML_ENCODE_PER_FRAME", "1") != "0"      # see encode_new_frames
         self.use_side_stream = os.environ.get("VFML_NO_SIDE_STREAM") is None
 
@@ -510,7 +513,13 @@ class MOFEngine:
         is in ring order: slot f = the window's centre frame (f - rot) mod Fc (rot = 0 unless the window slid, pyramid_ring)."""
         o = self.ops
         P = h * w
+        # the pyramids (store-bound volume kernel) are independent of the context rows + attention (GEMM + softmax): side stream
+        side = self.pyramid_side_stream and self.tiled and ws.get("fpyr") is not None
+        if side:
+            self._fork_side()
         fpyr, bpyr = self.build_pyramids(fmaps, ws, slide=slide, rot=rot)
+        if side:
+            self._back_to_main()
         x512 = ws["x512"]
         if rot:
             k = Fc - rot                  # centre frames k.. live in slots 0 .. rot-1, frames 0 .. k-1 in slots rot ..
@@ -523,6 +532,8 @@ class MOFEngine:
         if self.arch == "mof":
             o.rows_fill(ws["x400"][:, 352:400], self.init_mhs)      # init_hidden_state, stack.py:72-73
         self.attention(ws, Fc, P, [(Fc - 1 + rot) % Fc] if (slide and self.pyramid_ring) else None)
+        if side:
+            self._join_side()
         fc = o.coords_grid(Fc, h, w, self.dev)
         bc = o.coords_grid(Fc, h, w, self.dev)
         for _ in range(self.iters if iters is None else iters):
