@@ -591,7 +591,7 @@ def main():
     ap.add_argument("--iters", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip rooflines, fp32 tier, torch-on-GPU and CPU baselines")
-    ap.add_argument("--passes", type=int, default=int(os.environ.get("VFML_BENCH_PASSES", "3")),
+    ap.add_argument("--passes", type=int, default=int(os.environ.get("VFML_BENCH_PASSES", "5")),
                     help="independent timed passes of EXACTLY --steps steps each (fresh stretch of the clip per pass); the median pass is reported")
     args = ap.parse_args()
     if args.impl == "reference":
